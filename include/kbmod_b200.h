@@ -1,0 +1,155 @@
+/*
+ * kbmod_b200.h -- C-ABI of libkbmod_b200.so: KBMOD's shift-and-stack trajectory search for NVIDIA B200
+ * (sm_100a).  Plain pointers and sizes only; every function returns 0 on success and a non-zero code on
+ * failure, with the message available from kb_last_error() (the Python shim raises RuntimeError with it,
+ * matching the reference, whose errors are std::runtime_error -> RuntimeError).
+ *
+ * Each entry point names the reference interface it replaces (paths under src/kbmod/search/ of
+ * dirac-institute/kbmod @ 617cd33).  Host pointers are borrowed for the duration of the call only.
+ * A handle is bound to the CUDA device that was current when it was created and is not thread-safe
+ * (the reference object is not re-entrant either: stack_search.h:68-82 mutable results/params).
+ */
+#ifndef KBMOD_B200_H_
+#define KBMOD_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define KB_EXPORT __attribute__((visibility("default")))
+#else
+#define KB_EXPORT
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* common.h:55-67  struct Trajectory (28 bytes, tests/test_trajectory_list.py:28,47) */
+typedef struct {
+    float vx, vy, lh, flux;
+    int32_t x, y, obs_count;
+} kb_trajectory;
+
+/* common.h:119-161  struct SearchParameters */
+typedef struct {
+    int32_t min_observations;
+    float min_lh;
+    int32_t do_sigmag_filter;
+    float sgl_L, sgl_H, sigmag_coeff;
+    int32_t encode_num_bytes; /* -1, 1 or 2; informational, the stack knows its own encoding */
+    int32_t x_start_min, x_start_max, y_start_min, y_start_max;
+    uint32_t results_per_pixel;
+    uint64_t total_results;
+} kb_params;
+
+/* psi_phi_array_ds.h:50-69  struct PsiPhiArrayMeta */
+typedef struct {
+    uint64_t num_times, width, height, pixels_per_image, num_entries, block_size, total_array_size;
+    int32_t num_bytes; /* 4 (float), 2 (uint16), 1 (uint8) */
+    float psi_min_val, psi_max_val, psi_scale;
+    float phi_min_val, phi_max_val, phi_scale;
+} kb_meta;
+
+/* Device-side timings of the last kb_search on a handle (CUDA events on the handle's stream). */
+typedef struct {
+    float ms_h2d;          /* stack upload when not preloaded (psi_phi_array.cpp:74-111 move_to_gpu) */
+    float ms_prepare;      /* candidate upload + schedule construction */
+    float ms_search;       /* the search kernel(s) (kernels.cu:252-332 searchFilterImages) */
+    float ms_filter_sort;  /* filter + compaction + sort + gather (stack_search.cpp:268-277) */
+    float ms_total;        /* everything between entry and the last kernel, on the device */
+    uint64_t evals;        /* start pixels * candidates * times of that search */
+    uint32_t search_launches; /* number of search-kernel launches */
+    uint32_t total_launches;  /* all kernels launched by the call */
+    uint32_t used_tiled;      /* 1 when the TMA-staged tiled kernel ran, 0 for the generic kernel */
+    uint32_t reserved;
+} kb_timing;
+
+typedef struct kb_stack_s *kb_handle;
+
+/* ---- library ---------------------------------------------------------------------------------- */
+KB_EXPORT const char *kb_last_error(void);
+KB_EXPORT const char *kb_version(void);
+/* kernel_helpers.cpp:23-29 has_gpu() / kernels/kernel_memory.cu:15-60 */
+KB_EXPORT int kb_device_count(int *count);
+KB_EXPORT int kb_gpu_memory(size_t *free_bytes, size_t *total_bytes);
+
+/* ---- image operations (image_utils_cpp.cpp) ------------------------------------------------------ */
+/* convolve_image_gpu (:70-101) with the arithmetic of convolve_image_cpu (:20-68): mask-aware correlation,
+ * renormalised by the PSF portion used; NaN when no tap contributes. img/out: H*W float32; psf: dim*dim. */
+KB_EXPORT int kb_convolve(const float *img, int H, int W, const float *psf, int psf_dim, float *out);
+/* generate_psi (:126-153) and generate_phi (:155-177), fused: psi = conv(sci/var, psf), phi = conv(1/var, psf^2).
+ * Either output pointer may be NULL. */
+KB_EXPORT int kb_generate_psi_phi(const float *sci, const float *var, int H, int W, const float *psf, int psf_dim,
+                        float *psi_out, float *phi_out);
+
+/* ---- psi/phi stack (psi_phi_array.cpp, PsiPhiArray) ---------------------------------------------- */
+/* StackSearch ctor (stack_search.cpp:37-75) -> fill_psi_phi_array_from_image_arrays (psi_phi_array.cpp:374-410).
+ * sci/var: T pointers to H*W float32 images; psf: T pointers to psf_dim[t]^2 float32 kernels;
+ * num_bytes in {-1, 4, 2, 1}. Builds psi/phi and the encoded array on the device, keeps a host copy in the
+ * reference layout [t][row][col][psi,phi]. */
+KB_EXPORT int kb_create_from_images(const float *const *sci, const float *const *var, const float *const *psf,
+                          const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
+                          kb_handle *out);
+/* fill_psi_phi_array (psi_phi_array.cpp:321-372): from precomputed psi/phi images. */
+KB_EXPORT int kb_create_from_psi_phi(const float *const *psi, const float *const *phi, int T, int H, int W,
+                           const double *zeroed_times, int num_bytes, kb_handle *out);
+KB_EXPORT int kb_destroy(kb_handle h);
+KB_EXPORT int kb_get_meta(kb_handle h, kb_meta *meta);
+/* PsiPhiArray::get_cpu_array_ptr (psi_phi_array_ds.h:120): borrowed pointer to the host copy. */
+KB_EXPORT int kb_host_array(kb_handle h, const void **ptr, uint64_t *nbytes);
+/* PsiPhiArray::read_psi_phi (psi_phi_array.cpp:172-205), read_time (:207-212). Out of bounds -> NaN pair. */
+KB_EXPORT int kb_read_psi_phi(kb_handle h, uint64_t t, int row, int col, float out[2]);
+KB_EXPORT int kb_read_time(kb_handle h, uint64_t t, double *out);
+/* StackSearch::preload_psi_phi_array / unload_psi_phi_array / psi_phi_array_on_gpu (stack_search.cpp:174-186). */
+KB_EXPORT int kb_preload(kb_handle h);
+KB_EXPORT int kb_unload(kb_handle h);
+KB_EXPORT int kb_on_gpu(kb_handle h, int *flag);
+
+/* ---- search (stack_search.cpp:221-284 search_all with on_gpu=true; kernels.cu:252-397) ----------- */
+/* Evaluates every (start pixel in bounds, candidate) pair with the reference's GPU-path semantics, keeps the
+ * best results_per_pixel per start pixel, drops lh < min_lh and obs_count < min_observations, and sorts by
+ * lh descending on the device.  n_results receives the number of surviving results, which stay on the
+ * device until read with kb_get_results.  Unlike the reference there is no 200-image limit. */
+KB_EXPORT int kb_search(kb_handle h, const kb_params *params, const float *vx, const float *vy, uint64_t n_candidates,
+              uint64_t *n_results);
+/* TrajectoryList::get_batch (trajectory_list.cpp:85-94): copy [start, start+count) to out; n_copied may be
+ * smaller at the end of the list. */
+KB_EXPORT int kb_get_results(kb_handle h, uint64_t start, uint64_t count, kb_trajectory *out, uint64_t *n_copied);
+KB_EXPORT int kb_num_results(kb_handle h, uint64_t *n);
+/* StackSearch::set_results / clear_results (stack_search.cpp:329-338). */
+KB_EXPORT int kb_set_results(kb_handle h, const kb_trajectory *list, uint64_t n);
+KB_EXPORT int kb_clear_results(kb_handle h);
+KB_EXPORT int kb_get_timing(kb_handle h, kb_timing *t);
+/* The raw K*P per-pixel slots of the last search in the reference's order ((y_i*sw + x_i)*K + r), i.e. what
+ * searchFilterImages leaves in `results` before the host filter (kernels.cu:285-301,322-330). Debug/tests. */
+KB_EXPORT int kb_get_slots(kb_handle h, kb_trajectory *out, uint64_t capacity, uint64_t *n_slots);
+/* 0 = choose automatically, 1 = force the generic kernel, 2 = force the tiled TMA kernel (error if unusable). */
+KB_EXPORT int kb_set_kernel_mode(kb_handle h, int mode);
+
+/* StackSearch::evaluate_single_trajectory(trj, use_kernel=true) (stack_search.cpp:193-209 -> evaluateTrajectory
+ * kernels.cu:154-242): fills lh, flux, obs_count of each trajectory in place, on the device.  keep_mask
+ * (optional, n*T bytes) receives 1 where an observation contributed to the final lh/flux. */
+KB_EXPORT int kb_evaluate_trajectories(kb_handle h, const kb_params *params, kb_trajectory *trjs, uint64_t n,
+                             uint8_t *keep_mask);
+/* StackSearch::get_all_psi_phi_curves (stack_search.cpp:14-31,302-318): out is n rows of 2*T float32
+ * (psi values then phi values; invalid -> 0). */
+KB_EXPORT int kb_psi_phi_curves(kb_handle h, const kb_trajectory *trjs, uint64_t n, float *out);
+/* sigmag_filtered_indices test wrapper (kernel_helpers.cpp:86-106) evaluated by the device routine the search
+ * kernel uses: returns the indices kept, in ascending-value order. idx_out has room for n ints. */
+KB_EXPORT int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl1, float coeff, float width,
+                               int *idx_out, int *n_kept);
+
+/* ---- multi-GPU merge (no reference counterpart: the reference is single-GPU) ---------------------- */
+/* One process per GPU.  Rank 0 calls kb_nccl_unique_id and ships the 128 bytes to the other ranks by any
+ * means; every rank then calls kb_nccl_init.  kb_search_merge_topn all-gathers every rank's sorted results
+ * over NCCL and leaves the global best `top_n` (0 = all) as this handle's result list on every rank. */
+KB_EXPORT int kb_nccl_unique_id(uint8_t id[128]);
+KB_EXPORT int kb_nccl_init(const uint8_t id[128], int rank, int world_size);
+KB_EXPORT int kb_nccl_finalize(void);
+KB_EXPORT int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KBMOD_B200_H_ */

@@ -1,0 +1,724 @@
+// api.cu -- the C-ABI of libkbmod_b200.so (include/kbmod_b200.h): handle management, host orchestration of
+// StackSearch (stack_search.cpp) and PsiPhiArray (psi_phi_array.cpp) on top of the kernels in this directory.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <memory>
+
+#include "common.cuh"
+
+namespace kb {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string &msg) { g_last_error = msg; }
+
+template <typename T>
+struct DevBuf {  // RAII device buffer that only grows
+    T *p = nullptr;
+    uint64_t cap = 0;
+    void ensure(uint64_t n) {
+        if (n <= cap) return;
+        release();
+        KB_CUDA(cudaMalloc(&p, sizeof(T) * n));
+        cap = n;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    ~DevBuf() { release(); }
+};
+
+struct Timer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    Timer() {
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+    }
+    ~Timer() {
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+    }
+    void start(cudaStream_t st) { cudaEventRecord(a, st); }
+    void stop(cudaStream_t st) { cudaEventRecord(b, st); }
+    float ms() {
+        float m = 0.f;
+        cudaEventSynchronize(b);
+        cudaEventElapsedTime(&m, a, b);
+        return m;
+    }
+};
+
+}  // namespace kb
+
+using namespace kb;
+
+struct kb_stack_s {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int T = 0, H = 0, W = 0, Wp = 0, nb = 4;
+    kb_meta meta{};
+    std::vector<double> times;
+    void *host_array = nullptr;  // reference layout [t][row][col][psi,phi]
+    bool host_pinned = false;
+    void *d_search = nullptr;  // canonical pitched search copy
+    double *d_times = nullptr;
+    bool on_gpu = false;
+    int kernel_mode = 0;
+    // search state
+    DevBuf<float> d_vx, d_vy;
+    DevBuf<Slot> d_slots;
+    uint64_t n_slots = 0;
+    kb_params last_params{};
+    bool have_slots = false;
+    DevBuf<kb_trajectory> d_results, d_tmp;
+    uint64_t n_results = 0;
+    ResultScratch scratch;
+    kb_timing timing{};
+};
+
+static size_t pair_bytes(int nb) { return 2 * (size_t)nb; }
+
+static void use_device(kb_handle h) { KB_CUDA(cudaSetDevice(h->device)); }
+
+static StackView make_view(kb_handle h) {
+    StackView sv;
+    sv.data = h->d_search;
+    sv.times = h->d_times;
+    sv.T = h->T;
+    sv.H = h->H;
+    sv.W = h->W;
+    sv.Wp = h->Wp;
+    sv.nb = h->nb;
+    sv.psi_min = h->meta.psi_min_val;
+    sv.psi_scale = h->meta.psi_scale;
+    sv.phi_min = h->meta.phi_min_val;
+    sv.phi_scale = h->meta.phi_scale;
+    return sv;
+}
+
+static void alloc_host_array(kb_handle h, size_t bytes) {
+    const char *nopin = getenv("KB_NO_PIN");
+    if (!(nopin && nopin[0] == '1')) {
+        if (cudaHostAlloc(&h->host_array, bytes, cudaHostAllocDefault) == cudaSuccess) {
+            h->host_pinned = true;
+            return;
+        }
+        cudaGetLastError();
+    }
+    h->host_array = malloc(bytes);
+    h->host_pinned = false;
+    if (!h->host_array) throw Error("Unable to allocate space for CPU PsiPhi array.");
+}
+
+// PsiPhiArray::set_meta_data (psi_phi_array.cpp:113-148)
+static void set_meta(kb_handle h, int num_bytes, int T, int H, int W) {
+    if (num_bytes != -1 && num_bytes != 1 && num_bytes != 2 && num_bytes != 4)
+        throw Error("Invalid setting of num_bytes. Must be (-1 [use default], 1, 2, or 4). Got " +
+                    std::to_string(num_bytes));
+    if (T <= 0) throw Error("Invalid num_times passed to set_meta_data: " + std::to_string(T));
+    if (W <= 0) throw Error("Invalid width passed to set_meta_data: " + std::to_string(W));
+    if (H <= 0) throw Error("Invalid height passed to set_meta_data: " + std::to_string(H));
+    h->nb = (num_bytes == 1 || num_bytes == 2) ? num_bytes : 4;
+    h->T = T;
+    h->H = H;
+    h->W = W;
+    h->Wp = (W + 15) / 16 * 16;
+    kb_meta &m = h->meta;
+    m.num_bytes = h->nb;
+    m.block_size = h->nb;
+    m.num_times = T;
+    m.width = W;
+    m.height = H;
+    m.pixels_per_image = (uint64_t)W * H;
+    m.num_entries = 2 * m.pixels_per_image * T;
+    m.total_array_size = m.block_size * m.num_entries;
+    m.psi_min_val = m.phi_min_val = 3.402823466e+38F;
+    m.psi_max_val = m.phi_max_val = -3.402823466e+38F;
+    m.psi_scale = m.phi_scale = 1.0f;
+}
+
+// compute_scale_params_from_image_vect (psi_phi_array.cpp:219-245), given min/max from the device reduction.
+static void scale_from_minmax(float mn, float mx, int nb, float out[3]) {
+    float scale = 1.0f;
+    if (nb == 1 || nb == 2) {
+        float width = mx - mn;
+        if (width < 1e-6) width = 1e-6;
+        const uint64_t num_values = (1u << (8 * nb)) - 1;
+        scale = (float)((double)width / (double)num_values);
+    }
+    out[0] = mn;
+    out[1] = mx;
+    out[2] = scale;
+}
+
+// Given the float2 psi/phi stack on the device (reference order, unpitched), produce the host array in the
+// requested encoding (fill_psi_phi_array, psi_phi_array.cpp:321-372).
+static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
+    const uint64_t npix = (uint64_t)h->T * h->H * h->W;
+    alloc_host_array(h, h->meta.total_array_size);
+    if (h->nb == 4) {
+        KB_CUDA(cudaMemcpyAsync(h->host_array, d_pairs, h->meta.total_array_size, cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        DevBuf<uint32_t> d_mm;
+        d_mm.ensure(4);
+        launch_minmax(d_pairs, npix, d_mm.p, h->stream);
+        uint32_t mm[4];
+        KB_CUDA(cudaMemcpyAsync(mm, d_mm.p, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
+        KB_CUDA(cudaStreamSynchronize(h->stream));
+        // No finite value at all: the reference keeps min = FLT_MAX, max = -FLT_MAX (:223-232).
+        float pmn = 3.402823466e+38F, pmx = -3.402823466e+38F, fmn = pmn, fmx = pmx;
+        if (mm[0] <= mm[1]) { pmn = ordered_to_float(mm[0]); pmx = ordered_to_float(mm[1]); }
+        if (mm[2] <= mm[3]) { fmn = ordered_to_float(mm[2]); fmx = ordered_to_float(mm[3]); }
+        float pp[3], fp[3];
+        scale_from_minmax(pmn, pmx, h->nb, pp);
+        scale_from_minmax(fmn, fmx, h->nb, fp);
+        // PsiPhiArray::set_psi_scaling / set_phi_scaling checks (psi_phi_array.cpp:150-168)
+        if (pp[0] > pp[1]) throw Error("Min value needs to be < max value. Got " + std::to_string(pp[0]) + " and " + std::to_string(pp[1]));
+        if (fp[0] > fp[1]) throw Error("Min value needs to be < max value. Got " + std::to_string(fp[0]) + " and " + std::to_string(fp[1]));
+        h->meta.psi_min_val = pp[0]; h->meta.psi_max_val = pp[1]; h->meta.psi_scale = pp[2];
+        h->meta.phi_min_val = fp[0]; h->meta.phi_max_val = fp[1]; h->meta.phi_scale = fp[2];
+        DevBuf<uint8_t> d_enc;
+        d_enc.ensure(h->meta.total_array_size);
+        launch_encode(d_pairs, npix, h->nb, pp, fp, d_enc.p, h->stream);
+        KB_CUDA(cudaMemcpyAsync(h->host_array, d_enc.p, h->meta.total_array_size, cudaMemcpyDeviceToHost, h->stream));
+        KB_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    h->times.assign(times, times + h->T);
+}
+
+static kb_handle new_handle() {
+    std::unique_ptr<kb_stack_s> h(new kb_stack_s());
+    int cnt = 0;
+    if (cudaGetDeviceCount(&cnt) != cudaSuccess || cnt == 0) {
+        cudaGetLastError();
+        throw Error("GPU is not available (kbmod_b200 has no CPU fallback).");
+    }
+    KB_CUDA(cudaGetDevice(&h->device));
+    KB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    return h.release();
+}
+
+static void free_device_stack(kb_handle h) {
+    if (h->d_search) cudaFree(h->d_search);
+    if (h->d_times) cudaFree(h->d_times);
+    h->d_search = nullptr;
+    h->d_times = nullptr;
+    h->on_gpu = false;
+}
+
+static void destroy_handle(kb_handle h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    free_device_stack(h);
+    if (h->host_array) {
+        if (h->host_pinned) cudaFreeHost(h->host_array); else free(h->host_array);
+    }
+    result_scratch_free(h->scratch);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+// PsiPhiArray::move_to_gpu (psi_phi_array.cpp:74-111): upload + canonicalise into the pitched search copy.
+static void upload_stack(kb_handle h) {
+    if (h->on_gpu) return;
+    const size_t pb = pair_bytes(h->nb);
+    const size_t rows = (size_t)h->T * h->H;
+    KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
+    KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
+    KB_CUDA(cudaMemcpy2DAsync(h->d_search, (size_t)h->Wp * pb, h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, rows,
+                              cudaMemcpyHostToDevice, h->stream));
+    launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->stream);
+    h->on_gpu = true;
+}
+
+static void check_params(kb_handle h, const kb_params *p) {
+    if (p->x_start_min >= p->x_start_max)
+        throw Error("Invalid search bounds for the x pixel [" + std::to_string(p->x_start_min) + ", " +
+                    std::to_string(p->x_start_max) + "]");
+    if (p->y_start_min >= p->y_start_max)
+        throw Error("Invalid search bounds for the y pixel [" + std::to_string(p->y_start_min) + ", " +
+                    std::to_string(p->y_start_max) + "]");
+    if (p->results_per_pixel == 0) throw Error("Invalid results per pixel. Got 0");
+    if (p->min_observations < 0) throw Error("min_obs must be >= 0. Got " + std::to_string(p->min_observations));
+    if (p->do_sigmag_filter) {
+        if (!(p->sgl_L < p->sgl_H) || p->sgl_L <= 0.0f || p->sgl_H >= 1.0f)
+            throw Error("Invalid percentiles for sigma G filtering. Got [" + std::to_string(p->sgl_L) + ", " +
+                        std::to_string(p->sgl_H) + "].");
+        if (p->sigmag_coeff <= 0.0f)
+            throw Error("Invalid coefficient for sigma G filtering. Got " + std::to_string(p->sigmag_coeff) + ".");
+    }
+    const int64_t lim = 1 << 22;  // index arithmetic is exact well inside this range
+    if (p->x_start_min < -lim || p->x_start_max > lim || p->y_start_min < -lim || p->y_start_max > lim)
+        throw Error("Search bounds are out of the supported range (+-4194304).");
+    (void)h;
+}
+
+extern "C" {
+
+const char *kb_last_error(void) { return g_last_error.c_str(); }
+const char *kb_version(void) { return "kbmod_b200 0.1 (sm_100a)"; }
+
+int kb_device_count(int *count) {
+    KB_API_BEGIN
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+        cudaGetLastError();
+        c = 0;
+    }
+    *count = c;
+    KB_API_END
+}
+
+int kb_gpu_memory(size_t *free_bytes, size_t *total_bytes) {
+    KB_API_BEGIN
+    KB_CUDA(cudaMemGetInfo(free_bytes, total_bytes));
+    KB_API_END
+}
+
+static float host_sum(const float *k, int n) {
+    float s = 0.0f;
+    for (int i = 0; i < n; ++i) s += k[i];  // image_utils_cpp.cpp:30-35 row-major float adds
+    return s;
+}
+
+int kb_convolve(const float *img, int H, int W, const float *psf, int psf_dim, float *out) {
+    KB_API_BEGIN
+    if (H <= 0 || W <= 0 || psf_dim <= 0) throw Error("Invalid image or PSF dimensions.");
+    const size_t n = (size_t)H * W;
+    DevBuf<float> d_in, d_out, d_psf;
+    d_in.ensure(n);
+    d_out.ensure(n);
+    d_psf.ensure((size_t)psf_dim * psf_dim);
+    KB_CUDA(cudaMemcpy(d_in.p, img, n * sizeof(float), cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(d_psf.p, psf, sizeof(float) * psf_dim * psf_dim, cudaMemcpyHostToDevice));
+    launch_convolve(d_in.p, H, W, d_psf.p, psf_dim, host_sum(psf, psf_dim * psf_dim), d_out.p, 0);
+    KB_CUDA(cudaMemcpy(out, d_out.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
+int kb_generate_psi_phi(const float *sci, const float *var, int H, int W, const float *psf, int psf_dim,
+                        float *psi_out, float *phi_out) {
+    KB_API_BEGIN
+    if (H <= 0 || W <= 0 || psf_dim <= 0) throw Error("Invalid image or PSF dimensions.");
+    const size_t n = (size_t)H * W, kn = (size_t)psf_dim * psf_dim;
+    std::vector<float> k2(kn);
+    for (size_t i = 0; i < kn; ++i) k2[i] = psf[i] * psf[i];  // square_psf_values (image_utils_cpp.cpp:110-120)
+    DevBuf<float> d_sci, d_var, d_psi, d_phi, d_k, d_k2;
+    d_sci.ensure(n); d_var.ensure(n); d_psi.ensure(n); d_phi.ensure(n); d_k.ensure(kn); d_k2.ensure(kn);
+    // generate_phi takes no science image: feed zeros so the psi half is simply unused.
+    if (sci) KB_CUDA(cudaMemcpy(d_sci.p, sci, n * sizeof(float), cudaMemcpyHostToDevice));
+    else KB_CUDA(cudaMemset(d_sci.p, 0, n * sizeof(float)));
+    KB_CUDA(cudaMemcpy(d_var.p, var, n * sizeof(float), cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(d_k.p, psf, kn * sizeof(float), cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(d_k2.p, k2.data(), kn * sizeof(float), cudaMemcpyHostToDevice));
+    launch_psi_phi(d_sci.p, d_var.p, H, W, d_k.p, d_k2.p, psf_dim, host_sum(psf, (int)kn), host_sum(k2.data(), (int)kn),
+                   nullptr, d_psi.p, d_phi.p, 0);
+    if (psi_out) KB_CUDA(cudaMemcpy(psi_out, d_psi.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (phi_out) KB_CUDA(cudaMemcpy(phi_out, d_phi.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
+int kb_create_from_images(const float *const *sci, const float *const *var, const float *const *psf,
+                          const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
+                          kb_handle *out) {
+    KB_API_BEGIN
+    if (T <= 0) throw Error("No images in the to process.");
+    kb_handle h = new_handle();
+    try {
+        set_meta(h, num_bytes, T, H, W);
+        const size_t n = (size_t)H * W;
+        DevBuf<float2> d_pairs;
+        d_pairs.ensure(n * T);
+        // Double-buffered staging: the H2D copy of image t+1 overlaps the convolution of image t.
+        DevBuf<float> d_sci[2], d_var[2], d_k[2], d_k2[2];
+        cudaStream_t copy_st;
+        KB_CUDA(cudaStreamCreateWithFlags(&copy_st, cudaStreamNonBlocking));
+        cudaEvent_t copied[2], consumed[2];
+        for (int i = 0; i < 2; ++i) {
+            d_sci[i].ensure(n);
+            d_var[i].ensure(n);
+            KB_CUDA(cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming));
+            KB_CUDA(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
+        }
+        std::vector<float> k2;
+        for (int t = 0; t < T; ++t) {
+            const int b = t & 1;
+            const int dim = psf_dim[t];
+            if (dim <= 0 || (dim & 1) == 0) throw Error("PSF kernels must be square with an odd dimension.");
+            const size_t kn = (size_t)dim * dim;
+            k2.resize(kn);
+            for (size_t i = 0; i < kn; ++i) k2[i] = psf[t][i] * psf[t][i];
+            if (t >= 2) KB_CUDA(cudaStreamWaitEvent(copy_st, consumed[b], 0));
+            d_k[b].ensure(kn);
+            d_k2[b].ensure(kn);
+            KB_CUDA(cudaMemcpyAsync(d_sci[b].p, sci[t], n * sizeof(float), cudaMemcpyHostToDevice, copy_st));
+            KB_CUDA(cudaMemcpyAsync(d_var[b].p, var[t], n * sizeof(float), cudaMemcpyHostToDevice, copy_st));
+            KB_CUDA(cudaMemcpyAsync(d_k[b].p, psf[t], kn * sizeof(float), cudaMemcpyHostToDevice, copy_st));
+            KB_CUDA(cudaMemcpyAsync(d_k2[b].p, k2.data(), kn * sizeof(float), cudaMemcpyHostToDevice, copy_st));
+            KB_CUDA(cudaStreamSynchronize(copy_st));  // k2 is reused by the host next iteration
+            KB_CUDA(cudaEventRecord(copied[b], copy_st));
+            KB_CUDA(cudaStreamWaitEvent(h->stream, copied[b], 0));
+            launch_psi_phi(d_sci[b].p, d_var[b].p, H, W, d_k[b].p, d_k2[b].p, dim, host_sum(psf[t], (int)kn),
+                           host_sum(k2.data(), (int)kn), d_pairs.p + (size_t)t * n, nullptr, nullptr, h->stream);
+            KB_CUDA(cudaEventRecord(consumed[b], h->stream));
+        }
+        KB_CUDA(cudaStreamSynchronize(h->stream));
+        for (int i = 0; i < 2; ++i) {
+            cudaEventDestroy(copied[i]);
+            cudaEventDestroy(consumed[i]);
+        }
+        cudaStreamDestroy(copy_st);
+        finish_stack(h, d_pairs.p, zeroed_times);
+    } catch (...) {
+        destroy_handle(h);
+        throw;
+    }
+    *out = h;
+    KB_API_END
+}
+
+int kb_create_from_psi_phi(const float *const *psi, const float *const *phi, int T, int H, int W,
+                           const double *zeroed_times, int num_bytes, kb_handle *out) {
+    KB_API_BEGIN
+    if (T <= 0) throw Error("Trying to fill PsiPhi from empty vectors.");
+    kb_handle h = new_handle();
+    try {
+        set_meta(h, num_bytes, T, H, W);
+        const size_t n = (size_t)H * W;
+        DevBuf<float2> d_pairs;
+        d_pairs.ensure(n * T);
+        DevBuf<float> d_a, d_b;
+        d_a.ensure(n);
+        d_b.ensure(n);
+        for (int t = 0; t < T; ++t) {
+            KB_CUDA(cudaMemcpyAsync(d_a.p, psi[t], n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+            KB_CUDA(cudaMemcpyAsync(d_b.p, phi[t], n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+            launch_interleave(d_a.p, d_b.p, n, d_pairs.p + (size_t)t * n, h->stream);
+        }
+        finish_stack(h, d_pairs.p, zeroed_times);
+    } catch (...) {
+        destroy_handle(h);
+        throw;
+    }
+    *out = h;
+    KB_API_END
+}
+
+int kb_destroy(kb_handle h) {
+    KB_API_BEGIN
+    destroy_handle(h);
+    KB_API_END
+}
+
+int kb_get_meta(kb_handle h, kb_meta *meta) {
+    KB_API_BEGIN
+    *meta = h->meta;
+    KB_API_END
+}
+
+int kb_host_array(kb_handle h, const void **ptr, uint64_t *nbytes) {
+    KB_API_BEGIN
+    *ptr = h->host_array;
+    *nbytes = h->meta.total_array_size;
+    KB_API_END
+}
+
+int kb_read_psi_phi(kb_handle h, uint64_t t, int row, int col, float out[2]) {
+    KB_API_BEGIN
+    out[0] = out[1] = NAN;
+    if (!h->host_array || row < 0 || col < 0 || row >= h->H || col >= h->W || t >= (uint64_t)h->T) return 0;
+    const uint64_t idx = 2 * (h->meta.pixels_per_image * t + (uint64_t)row * h->W + (uint64_t)col);
+    if (h->nb == 4) {
+        out[0] = ((const float *)h->host_array)[idx];
+        out[1] = ((const float *)h->host_array)[idx + 1];
+    } else {
+        const float a = (h->nb == 1) ? (float)((const uint8_t *)h->host_array)[idx] : (float)((const uint16_t *)h->host_array)[idx];
+        const float b = (h->nb == 1) ? (float)((const uint8_t *)h->host_array)[idx + 1] : (float)((const uint16_t *)h->host_array)[idx + 1];
+        // decode_uint_scalar (psi_phi_array_ds.h:45-47)
+        out[0] = (a == 0.0f) ? NAN : (float)(((double)a - 1.0) * (double)h->meta.psi_scale + (double)h->meta.psi_min_val);
+        out[1] = (b == 0.0f) ? NAN : (float)(((double)b - 1.0) * (double)h->meta.phi_scale + (double)h->meta.phi_min_val);
+    }
+    KB_API_END
+}
+
+int kb_read_time(kb_handle h, uint64_t t, double *out) {
+    KB_API_BEGIN
+    if (t >= (uint64_t)h->T) throw Error("Out of bounds read for time step. [" + std::to_string(t) + "]");
+    *out = h->times[t];
+    KB_API_END
+}
+
+int kb_preload(kb_handle h) {
+    KB_API_BEGIN
+    use_device(h);
+    upload_stack(h);
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    KB_API_END
+}
+
+int kb_unload(kb_handle h) {
+    KB_API_BEGIN
+    use_device(h);
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    free_device_stack(h);
+    KB_API_END
+}
+
+int kb_on_gpu(kb_handle h, int *flag) {
+    KB_API_BEGIN
+    *flag = h->on_gpu ? 1 : 0;
+    KB_API_END
+}
+
+int kb_set_kernel_mode(kb_handle h, int mode) {
+    KB_API_BEGIN
+    if (mode < 0 || mode > 2) throw Error("kernel mode must be 0, 1 or 2");
+    h->kernel_mode = mode;
+    KB_API_END
+}
+
+int kb_search(kb_handle h, const kb_params *params, const float *vx, const float *vy, uint64_t n_cand,
+              uint64_t *n_results) {
+    KB_API_BEGIN
+    use_device(h);
+    check_params(h, params);
+    if (params->min_observations > h->T)
+        throw Error("min_obs cannot be greater than the number of images. min_obs = " +
+                    std::to_string(params->min_observations) + ", num_imgs = " + std::to_string(h->T) + ".");
+    for (uint64_t i = 0; i < n_cand; ++i)  // TrajectoryList::assert_valid (trajectory_list.cpp:155-164)
+        if (!isfinite(vx[i]) || !isfinite(vy[i]))
+            throw Error("Invalid trajectory detected at index " + std::to_string(i));
+    if (n_cand >= (1ull << 31)) throw Error("Too many candidate trajectories.");
+    kb_params p = *params;
+    const uint64_t sw = (uint64_t)(p.x_start_max - p.x_start_min), sh = (uint64_t)(p.y_start_max - p.y_start_min);
+    const uint64_t n_slots = sw * sh * p.results_per_pixel;
+    p.total_results = n_slots;
+    h->timing = kb_timing{};
+    h->timing.evals = sw * sh * n_cand * (uint64_t)h->T;
+    cudaStream_t st = h->stream;
+    Timer t_total, t_h2d, t_prep, t_search, t_post;
+    uint32_t launches = 0;
+
+    t_total.start(st);
+    const bool was_on_gpu = h->on_gpu;
+    t_h2d.start(st);
+    if (!was_on_gpu) { upload_stack(h); launches += 1; }
+    t_h2d.stop(st);
+
+    t_prep.start(st);
+    h->d_vx.ensure(std::max<uint64_t>(n_cand, 1));
+    h->d_vy.ensure(std::max<uint64_t>(n_cand, 1));
+    if (n_cand) {
+        KB_CUDA(cudaMemcpyAsync(h->d_vx.p, vx, sizeof(float) * n_cand, cudaMemcpyHostToDevice, st));
+        KB_CUDA(cudaMemcpyAsync(h->d_vy.p, vy, sizeof(float) * n_cand, cudaMemcpyHostToDevice, st));
+    }
+    h->d_slots.ensure(n_slots);
+    const StackView sv = make_view(h);
+    TiledPlan *plan = nullptr;
+    std::string why;
+    if (h->kernel_mode != 1) {
+        plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why);
+        if (!plan && h->kernel_mode == 2) throw Error("tiled kernel not usable: " + why);
+    }
+    t_prep.stop(st);
+
+    t_search.start(st);
+    uint32_t sl = 0;
+    try {
+        if (plan) sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, st);
+        else sl = launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
+    } catch (...) {
+        if (plan) tiled_plan_destroy(plan);
+        throw;
+    }
+    t_search.stop(st);
+    launches += sl;
+    h->timing.search_launches = sl;
+    h->timing.used_tiled = plan ? 1 : 0;
+
+    t_post.start(st);
+    uint64_t n_keep = 0;
+    launches += filter_count(h->d_slots.p, n_slots, p.min_lh, p.min_observations, h->scratch, &n_keep, st);
+    if (plan) tiled_plan_destroy(plan);  // the stream is idle here (filter_count synchronised)
+    h->d_results.ensure(std::max<uint64_t>(n_keep, 1));
+    bool invalid = false;
+    launches += filter_finish(h->d_slots.p, n_slots, n_keep, (int)p.results_per_pixel, (int)sw, p.x_start_min,
+                              p.y_start_min, p.min_lh, p.min_observations, h->d_vx.p, h->d_vy.p, h->scratch,
+                              h->d_results.p, &invalid, st);
+    t_post.stop(st);
+    t_total.stop(st);
+    KB_CUDA(cudaStreamSynchronize(st));
+    h->n_results = n_keep;
+    h->n_slots = n_slots;
+    h->last_params = p;
+    h->have_slots = true;
+    h->timing.ms_h2d = t_h2d.ms();
+    h->timing.ms_prepare = t_prep.ms();
+    h->timing.ms_search = t_search.ms();
+    h->timing.ms_filter_sort = t_post.ms();
+    h->timing.ms_total = t_total.ms();
+    h->timing.total_launches = launches;
+    if (!was_on_gpu) free_device_stack(h);  // search_all frees the stack again unless preloaded (:257)
+    if (invalid) throw Error("Invalid trajectory detected in the search results.");
+    if (n_results) *n_results = n_keep;
+    KB_API_END
+}
+
+int kb_num_results(kb_handle h, uint64_t *n) {
+    KB_API_BEGIN
+    *n = h->n_results;
+    KB_API_END
+}
+
+int kb_get_results(kb_handle h, uint64_t start, uint64_t count, kb_trajectory *out, uint64_t *n_copied) {
+    KB_API_BEGIN
+    use_device(h);
+    if (count == 0) throw Error("count must be greater than 0");
+    uint64_t n = 0;
+    if (start < h->n_results) n = std::min(count, h->n_results - start);
+    if (n) KB_CUDA(cudaMemcpy(out, h->d_results.p + start, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToHost));
+    if (n_copied) *n_copied = n;
+    KB_API_END
+}
+
+int kb_set_results(kb_handle h, const kb_trajectory *list, uint64_t n) {
+    KB_API_BEGIN
+    use_device(h);
+    for (uint64_t i = 0; i < n; ++i) {
+        const kb_trajectory &t = list[i];
+        if (!(isfinite(t.vx) && isfinite(t.vy) && isfinite(t.lh) && isfinite(t.flux) && t.obs_count >= 0))
+            throw Error("Invalid trajectory detected at index " + std::to_string(i));
+    }
+    h->d_results.ensure(std::max<uint64_t>(n, 1));
+    if (n) KB_CUDA(cudaMemcpy(h->d_results.p, list, sizeof(kb_trajectory) * n, cudaMemcpyHostToDevice));
+    h->n_results = n;
+    KB_API_END
+}
+
+int kb_clear_results(kb_handle h) {
+    KB_API_BEGIN
+    h->n_results = 0;
+    KB_API_END
+}
+
+int kb_get_timing(kb_handle h, kb_timing *t) {
+    KB_API_BEGIN
+    *t = h->timing;
+    KB_API_END
+}
+
+int kb_get_slots(kb_handle h, kb_trajectory *out, uint64_t capacity, uint64_t *n_slots) {
+    KB_API_BEGIN
+    use_device(h);
+    if (!h->have_slots) throw Error("No search has been run on this handle.");
+    if (n_slots) *n_slots = h->n_slots;
+    if (!out) return 0;
+    if (capacity < h->n_slots) throw Error("Output buffer too small for the result slots.");
+    const kb_params &p = h->last_params;
+    h->d_tmp.ensure(h->n_slots);
+    slots_to_trajectories(h->d_slots.p, h->n_slots, (int)p.results_per_pixel, p.x_start_max - p.x_start_min,
+                          p.x_start_min, p.y_start_min, h->d_vx.p, h->d_vy.p, h->d_tmp.p, h->stream);
+    KB_CUDA(cudaMemcpyAsync(out, h->d_tmp.p, sizeof(kb_trajectory) * h->n_slots, cudaMemcpyDeviceToHost, h->stream));
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    KB_API_END
+}
+
+int kb_evaluate_trajectories(kb_handle h, const kb_params *params, kb_trajectory *trjs, uint64_t n,
+                             uint8_t *keep_mask) {
+    KB_API_BEGIN
+    use_device(h);
+    if (n == 0) return 0;
+    const bool was_on_gpu = h->on_gpu;
+    if (!was_on_gpu) upload_stack(h);
+    DevBuf<kb_trajectory> d_t;
+    DevBuf<uint8_t> d_m;
+    d_t.ensure(n);
+    if (keep_mask) d_m.ensure(n * (uint64_t)h->T);
+    KB_CUDA(cudaMemcpyAsync(d_t.p, trjs, sizeof(kb_trajectory) * n, cudaMemcpyHostToDevice, h->stream));
+    launch_evaluate(make_view(h), *params, d_t.p, n, keep_mask ? d_m.p : nullptr, h->stream);
+    KB_CUDA(cudaMemcpyAsync(trjs, d_t.p, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToHost, h->stream));
+    if (keep_mask)
+        KB_CUDA(cudaMemcpyAsync(keep_mask, d_m.p, n * (uint64_t)h->T, cudaMemcpyDeviceToHost, h->stream));
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    if (!was_on_gpu) free_device_stack(h);
+    KB_API_END
+}
+
+int kb_psi_phi_curves(kb_handle h, const kb_trajectory *trjs, uint64_t n, float *out) {
+    KB_API_BEGIN
+    use_device(h);
+    if (n == 0) return 0;
+    // The curves are read from the reference-layout array (psi and phi validity are independent there).
+    // Pinned host memory is directly addressable by the device (UVA); otherwise stage a temporary copy.
+    DevBuf<uint8_t> d_raw;
+    const void *src = h->host_array;
+    if (!h->host_pinned) {
+        d_raw.ensure(h->meta.total_array_size);
+        KB_CUDA(cudaMemcpyAsync(d_raw.p, h->host_array, h->meta.total_array_size, cudaMemcpyHostToDevice, h->stream));
+        src = d_raw.p;
+    }
+    DevBuf<kb_trajectory> d_t;
+    DevBuf<float> d_out;
+    DevBuf<double> d_times;
+    d_t.ensure(n);
+    d_out.ensure(n * 2 * (uint64_t)h->T);
+    d_times.ensure(h->T);
+    KB_CUDA(cudaMemcpyAsync(d_times.p, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
+    KB_CUDA(cudaMemcpyAsync(d_t.p, trjs, sizeof(kb_trajectory) * n, cudaMemcpyHostToDevice, h->stream));
+    launch_curves(src, d_times.p, h->T, h->H, h->W, h->nb, h->meta.psi_min_val, h->meta.psi_scale,
+                  h->meta.phi_min_val, h->meta.phi_scale, d_t.p, n, d_out.p, h->stream);
+    KB_CUDA(cudaMemcpyAsync(out, d_out.p, sizeof(float) * n * 2 * (uint64_t)h->T, cudaMemcpyDeviceToHost, h->stream));
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    KB_API_END
+}
+
+int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl1, float coeff, float width,
+                               int *idx_out, int *n_kept) {
+    KB_API_BEGIN
+    *n_kept = 0;
+    if (n <= 0) return 0;
+    DevBuf<float> d_v;
+    DevBuf<int> d_idx, d_range;
+    d_v.ensure(n);
+    d_idx.ensure(n);
+    d_range.ensure(2);
+    KB_CUDA(cudaMemcpy(d_v.p, values, sizeof(float) * n, cudaMemcpyHostToDevice));
+    launch_sigmag_indices(d_v.p, n, sgl0, sgl1, coeff, width, d_idx.p, d_range.p, 0);
+    int range[2];
+    std::vector<int> idx(n);
+    KB_CUDA(cudaMemcpy(range, d_range.p, sizeof(range), cudaMemcpyDeviceToHost));
+    KB_CUDA(cudaMemcpy(idx.data(), d_idx.p, sizeof(int) * n, cudaMemcpyDeviceToHost));
+    int k = 0;
+    for (int i = range[0]; i <= range[1] && i < n; ++i)
+        if (i >= 0) idx_out[k++] = idx[i];
+    *n_kept = k;
+    KB_API_END
+}
+
+}  // extern "C"
+
+// ---- accessors used by nccl_merge.cu ------------------------------------------------------------------
+namespace kb {
+cudaStream_t handle_stream(kb_handle h) { return h->stream; }
+int handle_device(kb_handle h) { return h->device; }
+kb_trajectory *handle_results(kb_handle h, uint64_t *n) {
+    *n = h->n_results;
+    return h->d_results.p;
+}
+void handle_replace_results(kb_handle h, const kb_trajectory *d_src, uint64_t n, bool sort) {
+    h->d_tmp.ensure(std::max<uint64_t>(n, 1));
+    if (d_src != h->d_results.p) {
+        h->d_results.ensure(std::max<uint64_t>(n, 1));
+        if (n) KB_CUDA(cudaMemcpyAsync(h->d_results.p, d_src, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToDevice, h->stream));
+    }
+    if (sort) sort_trajectories_by_lh(h->d_results.p, n, h->scratch, h->d_tmp.p, h->stream);
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    h->n_results = n;
+}
+}  // namespace kb

@@ -1,0 +1,128 @@
+// common.cuh -- internal declarations shared by the translation units of libkbmod_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/kbmod_b200.h"
+
+namespace kb {
+
+// ---- error plumbing -------------------------------------------------------------------------------
+void set_error(const std::string &msg);
+
+struct Error : public std::runtime_error {
+    explicit Error(const std::string &m) : std::runtime_error(m) {}
+};
+
+#define KB_CUDA(expr)                                                                                  \
+    do {                                                                                               \
+        cudaError_t _e = (expr);                                                                       \
+        if (_e != cudaSuccess)                                                                         \
+            throw kb::Error(std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + __FILE__ + \
+                            ":" + std::to_string(__LINE__) + " (" #expr ")");                          \
+    } while (0)
+
+#define KB_API_BEGIN try {
+#define KB_API_END                          \
+    }                                       \
+    catch (const std::exception &e) {       \
+        kb::set_error(e.what());            \
+        return 1;                           \
+    }                                       \
+    catch (...) {                           \
+        kb::set_error("unknown error");     \
+        return 2;                           \
+    }                                       \
+    return 0;
+
+// ---- device view of the psi/phi stack ----------------------------------------------------------------
+// Search copy in HBM: [t][row][Wp] pixel pairs (psi, phi); pair = float2 / ushort2 / uchar2.  Rows are padded
+// to Wp pixels so the row pitch is a multiple of 16 bytes (TMA global-stride rule).  Pairs are canonical:
+// if either member is invalid (non-finite float, code 0) both are (NaN,NaN) / (0,0), so one test decides
+// whether the observation counts (kernels.cu:184: both must be finite).
+struct StackView {
+    const void *data;
+    const double *times;
+    int T, H, W, Wp;
+    int nb;  // bytes per value: 4, 2, 1
+    float psi_min, psi_scale, phi_min, phi_scale;
+};
+
+// Per-pixel result slot written by the search kernels: 16 bytes, [pixel][K].
+struct __align__(16) Slot {
+    float lh;
+    float flux;
+    int obs;
+    int cand;  // candidate index, -1 = empty slot
+};
+
+static constexpr int kMaxRegK = 8;      // results_per_pixel kept in registers
+static constexpr int kMaxTSigma = 1024; // largest T for which the in-kernel sigma-G path is instantiated
+
+// ---- launchers (each returns the number of kernels it launched) ------------------------------------
+// search_generic.cu
+int launch_search_generic(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
+                          uint64_t n_cand, Slot *d_slots, cudaStream_t st);
+int launch_evaluate(const StackView &sv, const kb_params &p, kb_trajectory *d_trjs, uint64_t n, uint8_t *d_mask,
+                    cudaStream_t st);
+int launch_sigmag_indices(const float *d_vals, int n, float sgl0, float sgl1, float coeff, float width, int *d_idx,
+                          int *d_range, cudaStream_t st);
+int launch_curves(const void *d_ref_layout, const double *d_times, int T, int H, int W, int nb, float psi_min,
+                  float psi_scale, float phi_min, float phi_scale, const kb_trajectory *d_trjs, uint64_t n,
+                  float *d_out, cudaStream_t st);
+
+// search_tiled.cu
+struct TiledPlan;  // opaque: schedule for the TMA-staged kernel
+// Returns nullptr (and a reason) when the tiled kernel cannot be used for this search.
+TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not);
+int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
+                        const float *d_vy, Slot *d_slots, cudaStream_t st);
+void tiled_plan_destroy(TiledPlan *plan);
+
+// psi_phi.cu
+int launch_convolve(const float *d_img, int H, int W, const float *d_psf, int dim, float psf_total, float *d_out,
+                    cudaStream_t st);
+// psi/phi for one image, written interleaved (float2) at d_out_pairs[H*W]; or to separate planes.
+int launch_psi_phi(const float *d_sci, const float *d_var, int H, int W, const float *d_psf, const float *d_psf2,
+                   int dim, float psf_total, float psf2_total, float2 *d_out_pairs, float *d_psi_plane,
+                   float *d_phi_plane, cudaStream_t st);
+int launch_interleave(const float *d_psi, const float *d_phi, uint64_t n, float2 *d_out, cudaStream_t st);
+// min/max over finite values of both channels: d_mm = {psi_min, psi_max, phi_min, phi_max} as ordered uints.
+int launch_minmax(const float2 *d_pairs, uint64_t n, uint32_t *d_mm, cudaStream_t st);
+int launch_encode(const float2 *d_pairs, uint64_t n, int nb, const float psi_p[3], const float phi_p[3], void *d_out,
+                  cudaStream_t st);
+// rows of `src_pitch` pixel pairs -> canonical search copy with pitch Wp (in place when src == dst and pitches match).
+int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
+                        cudaStream_t st);
+float ordered_to_float(uint32_t u);
+
+// results.cu
+struct ResultScratch {
+    uint32_t *keys[2] = {nullptr, nullptr};
+    uint32_t *vals[2] = {nullptr, nullptr};
+    uint32_t *block_counts = nullptr;  // compaction
+    uint32_t *hist = nullptr;          // radix histograms
+    uint64_t cap_items = 0, cap_blocks = 0, cap_hist = 0;
+    uint32_t *d_count = nullptr;  // number of survivors
+    uint32_t *d_flag = nullptr;   // invalid-trajectory flag
+};
+void result_scratch_free(ResultScratch &s);
+// slots[P*K] -> filtered, sorted kb_trajectory list. Two phases so the caller can size the output:
+// filter_count() returns the number of survivors (syncs the stream); filter_finish() writes them to d_out.
+int filter_count(const Slot *d_slots, uint64_t n_slots, float min_lh, int min_obs, ResultScratch &scr,
+                 uint64_t *n_out, cudaStream_t st);
+int filter_finish(const Slot *d_slots, uint64_t n_slots, uint64_t n_keep, int K, int sw, int x0, int y0, float min_lh,
+                  int min_obs, const float *d_vx, const float *d_vy, ResultScratch &scr, kb_trajectory *d_out,
+                  bool *invalid, cudaStream_t st);
+int slots_to_trajectories(const Slot *d_slots, uint64_t n_slots, int K, int sw, int x0, int y0, const float *d_vx,
+                          const float *d_vy, kb_trajectory *d_out, cudaStream_t st);
+// Sort (key desc by lh) an existing device list of trajectories in place (used by the multi-GPU merge).
+int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &scr, kb_trajectory *d_tmp,
+                            cudaStream_t st);
+
+}  // namespace kb

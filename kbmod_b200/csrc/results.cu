@@ -1,0 +1,367 @@
+// results.cu -- device-side replacement of the host post-processing in StackSearch::search_all
+// (stack_search.cpp:268-277; trajectory_list.cpp:96-126): drop lh < min_lh, drop obs_count < min_obs, sort by
+// lh descending.  The reference ships all K*P records to the host and filters/sorts there; here the slots
+// stay in HBM, survivors are compacted with an order-preserving scan, sorted with a stable LSD radix sort
+// (hand-written, 8-bit digits, warp match-any ranking) and only then expanded to 28-byte Trajectory records.
+// Ties in lh keep slot order (y, x, rank): deterministic, where the reference's parallel sort is not.
+#include <float.h>
+
+#include "common.cuh"
+
+namespace kb {
+
+static constexpr int CB = 256, C_ITEMS = 4, C_TILE = CB * C_ITEMS;  // compaction tile
+static constexpr int RB = 256, R_WARPS = RB / 32, R_ITEMS = 16, R_TILE = RB * R_ITEMS;  // radix tile
+
+__device__ __forceinline__ bool slot_passes(const Slot &s, float min_lh, int min_obs) {
+    return !(s.lh < min_lh) && !(s.obs < min_obs);  // remove_if(lh < min_lh), remove_if(obs < min_obs)
+}
+
+// key: ascending unsigned order == descending lh
+__device__ __forceinline__ uint32_t lh_key(float lh) {
+    const uint32_t u = __float_as_uint(lh);
+    const uint32_t ordered = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    return ~ordered;
+}
+
+// exclusive rank of a 0/1 flag among the CB threads of the block + block total
+__device__ __forceinline__ uint32_t block_rank(bool flag, uint32_t *s_warp /*[CB/32]*/, uint32_t &total) {
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t bal = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_warp[w] = __popc(bal);
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int i = 0; i < CB / 32; ++i) {
+        const uint32_t c = s_warp[i];
+        if (i < (int)w) base += c;
+        tot += c;
+    }
+    __syncthreads();
+    total = tot;
+    return base + __popc(bal & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(CB) count_kernel(const Slot *__restrict__ slots, uint64_t n, float min_lh,
+                                                   int min_obs, uint32_t *__restrict__ block_counts) {
+    __shared__ uint32_t s_warp[CB / 32];
+    const uint64_t base = (uint64_t)blockIdx.x * C_TILE;
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int j = 0; j < C_ITEMS; ++j) {
+        const uint64_t i = base + (uint64_t)j * CB + threadIdx.x;
+        if (i < n && slot_passes(slots[i], min_lh, min_obs)) ++cnt;
+    }
+    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int i = 0; i < CB / 32; ++i) t += s_warp[i];
+        block_counts[blockIdx.x] = t;
+    }
+}
+
+// In-place exclusive scan of `n` uint32 by one CTA; total -> *total_out (may be null).
+__global__ void __launch_bounds__(1024) scan_kernel(uint32_t *data, uint64_t n, uint32_t *total_out) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint64_t base = 0; base < n; base += 1024) {
+        const uint64_t i = base + threadIdx.x;
+        const uint32_t v = (i < n) ? data[i] : 0u;
+        uint32_t inc = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if ((int)lane >= d) inc += t;
+        }
+        if (lane == 31) s_warp[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            uint32_t ws = s_warp[lane], winc = ws;
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, winc, d);
+                if ((int)lane >= d) winc += t;
+            }
+            s_warp[lane] = winc - ws;  // exclusive prefix of warp sums
+        }
+        __syncthreads();
+        const uint32_t carry = s_carry;
+        const uint32_t excl = carry + s_warp[w] + inc - v;
+        if (i < n) data[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && total_out) *total_out = s_carry;
+}
+
+__global__ void __launch_bounds__(CB)
+        compact_kernel(const Slot *__restrict__ slots, uint64_t n, float min_lh, int min_obs,
+                       const uint32_t *__restrict__ block_offsets, uint32_t *__restrict__ keys,
+                       uint32_t *__restrict__ vals) {
+    __shared__ uint32_t s_warp[CB / 32];
+    const uint64_t base = (uint64_t)blockIdx.x * C_TILE;
+    uint32_t out = block_offsets[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < C_ITEMS; ++j) {
+        const uint64_t i = base + (uint64_t)j * CB + threadIdx.x;
+        Slot s{0.f, 0.f, 0, -1};
+        bool keep = false;
+        if (i < n) {
+            s = slots[i];
+            keep = slot_passes(s, min_lh, min_obs);
+        }
+        uint32_t total;
+        const uint32_t r = block_rank(keep, s_warp, total);
+        if (keep) {
+            keys[out + r] = lh_key(s.lh);
+            vals[out + r] = (uint32_t)i;
+        }
+        out += total;
+    }
+}
+
+// ---- LSD radix sort, one 8-bit digit per pass ----------------------------------------------------------
+__global__ void __launch_bounds__(RB) radix_hist_kernel(const uint32_t *__restrict__ keys, uint64_t n, int shift,
+                                                        uint32_t *__restrict__ hist, uint32_t nblocks) {
+    __shared__ uint32_t s_h[256];
+    s_h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint64_t base = (uint64_t)blockIdx.x * R_TILE;
+#pragma unroll
+    for (int j = 0; j < R_ITEMS; ++j) {
+        const uint64_t i = base + (uint64_t)j * RB + threadIdx.x;
+        if (i < n) atomicAdd(&s_h[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[(uint64_t)threadIdx.x * nblocks + blockIdx.x] = s_h[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(RB)
+        radix_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in, uint64_t n,
+                             int shift, const uint32_t *__restrict__ hist_scanned, uint32_t nblocks,
+                             uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out) {
+    __shared__ uint32_t s_cnt[R_WARPS][256];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < R_WARPS * 256; i += RB) (&s_cnt[0][0])[i] = 0;
+    __syncthreads();
+
+    const uint64_t wbase = (uint64_t)blockIdx.x * R_TILE + (uint64_t)w * (R_ITEMS * 32);
+    uint32_t k[R_ITEMS], v[R_ITEMS], rk[R_ITEMS];
+#pragma unroll
+    for (int r = 0; r < R_ITEMS; ++r) {
+        const uint64_t i = wbase + (uint64_t)r * 32 + lane;
+        const bool valid = i < n;
+        k[r] = valid ? keys_in[i] : 0u;
+        v[r] = valid ? vals_in[i] : 0u;
+        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        rk[r] = 0;
+        if (valid) {
+            const uint32_t d = (k[r] >> shift) & 255u;
+            const uint32_t peers = __match_any_sync(vmask, d);
+            const int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if ((int)lane == leader) {
+                old = s_cnt[w][d];
+                s_cnt[w][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(peers, old, leader);
+            rk[r] = old + __popc(peers & ((1u << lane) - 1u));
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // thread d: turn per-warp counts of digit d into global destinations
+        const uint32_t d = threadIdx.x;
+        uint32_t run = hist_scanned[(uint64_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int ww = 0; ww < R_WARPS; ++ww) {
+            const uint32_t c = s_cnt[ww][d];
+            s_cnt[ww][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < R_ITEMS; ++r) {
+        const uint64_t i = wbase + (uint64_t)r * 32 + lane;
+        if (i < n) {
+            const uint32_t d = (k[r] >> shift) & 255u;
+            const uint32_t dst = s_cnt[w][d] + rk[r];
+            keys_out[dst] = k[r];
+            vals_out[dst] = v[r];
+        }
+    }
+}
+
+// keys/vals live in scr.keys[0]/vals[0]; after the 4 passes the sorted data is back in buffer 0.
+static int radix_sort_pairs(ResultScratch &scr, uint64_t n, cudaStream_t st) {
+    if (n <= 1) return 0;
+    const uint32_t nblocks = (uint32_t)((n + R_TILE - 1) / R_TILE);
+    int launches = 0, cur = 0;
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = pass * 8;
+        radix_hist_kernel<<<nblocks, RB, 0, st>>>(scr.keys[cur], n, shift, scr.hist, nblocks);
+        scan_kernel<<<1, 1024, 0, st>>>(scr.hist, (uint64_t)256 * nblocks, nullptr);
+        radix_scatter_kernel<<<nblocks, RB, 0, st>>>(scr.keys[cur], scr.vals[cur], n, shift, scr.hist, nblocks,
+                                                     scr.keys[cur ^ 1], scr.vals[cur ^ 1]);
+        cur ^= 1;
+        launches += 3;
+    }
+    KB_CUDA(cudaGetLastError());
+    return launches;
+}
+
+__device__ __forceinline__ kb_trajectory expand_slot(const Slot &s, uint64_t slot_index, int K, int sw, int x0,
+                                                     int y0, const float *vx, const float *vy) {
+    const uint64_t pix = slot_index / (uint64_t)K;
+    kb_trajectory t;
+    t.x = x0 + (int)(pix % (uint64_t)sw);
+    t.y = y0 + (int)(pix / (uint64_t)sw);
+    t.lh = s.lh;
+    t.flux = s.flux;
+    t.obs_count = s.obs;
+    t.vx = (s.cand >= 0) ? vx[s.cand] : 0.0f;
+    t.vy = (s.cand >= 0) ? vy[s.cand] : 0.0f;
+    return t;
+}
+
+__global__ void gather_kernel(const Slot *__restrict__ slots, const uint32_t *__restrict__ order, uint64_t n, int K,
+                              int sw, int x0, int y0, const float *__restrict__ vx, const float *__restrict__ vy,
+                              kb_trajectory *__restrict__ out, uint32_t *invalid_flag) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t si = order ? order[i] : i;
+    const kb_trajectory t = expand_slot(slots[si], si, K, sw, x0, y0, vx, vy);
+    // Trajectory::is_valid (common.h:100-102): search_all throws if a survivor is not finite.
+    if (invalid_flag && !(isfinite(t.lh) && isfinite(t.flux) && isfinite(t.vx) && isfinite(t.vy) && t.obs_count >= 0))
+        atomicExch(invalid_flag, 1u);
+    out[i] = t;
+}
+
+static void ensure_scratch(ResultScratch &s, uint64_t items, uint64_t cblocks) {
+    if (!s.d_count) {
+        KB_CUDA(cudaMalloc(&s.d_count, sizeof(uint32_t)));
+        KB_CUDA(cudaMalloc(&s.d_flag, sizeof(uint32_t)));
+    }
+    if (cblocks > s.cap_blocks) {
+        if (s.block_counts) cudaFree(s.block_counts);
+        s.block_counts = nullptr;
+        KB_CUDA(cudaMalloc(&s.block_counts, sizeof(uint32_t) * cblocks));
+        s.cap_blocks = cblocks;
+    }
+    if (items > s.cap_items) {
+        for (int i = 0; i < 2; ++i) {
+            if (s.keys[i]) cudaFree(s.keys[i]);
+            if (s.vals[i]) cudaFree(s.vals[i]);
+            s.keys[i] = s.vals[i] = nullptr;
+        }
+        s.cap_items = 0;
+        const uint64_t cap = items + items / 8 + 1024;
+        for (int i = 0; i < 2; ++i) {
+            KB_CUDA(cudaMalloc(&s.keys[i], sizeof(uint32_t) * cap));
+            KB_CUDA(cudaMalloc(&s.vals[i], sizeof(uint32_t) * cap));
+        }
+        s.cap_items = cap;
+    }
+    const uint64_t need_hist = 256 * ((items + R_TILE - 1) / R_TILE + 1);
+    if (need_hist > s.cap_hist) {
+        if (s.hist) cudaFree(s.hist);
+        s.hist = nullptr;
+        KB_CUDA(cudaMalloc(&s.hist, sizeof(uint32_t) * need_hist));
+        s.cap_hist = need_hist;
+    }
+}
+
+void result_scratch_free(ResultScratch &s) {
+    for (int i = 0; i < 2; ++i) {
+        if (s.keys[i]) cudaFree(s.keys[i]);
+        if (s.vals[i]) cudaFree(s.vals[i]);
+    }
+    if (s.block_counts) cudaFree(s.block_counts);
+    if (s.hist) cudaFree(s.hist);
+    if (s.d_count) cudaFree(s.d_count);
+    if (s.d_flag) cudaFree(s.d_flag);
+    s = ResultScratch();
+}
+
+int filter_count(const Slot *d_slots, uint64_t n_slots, float min_lh, int min_obs, ResultScratch &scr,
+                 uint64_t *n_out, cudaStream_t st) {
+    if (n_slots >= (1ull << 32)) throw Error("Too many result slots for 32-bit indices.");
+    const uint64_t cblocks = (n_slots + C_TILE - 1) / C_TILE;
+    ensure_scratch(scr, 0, cblocks);
+    count_kernel<<<(unsigned)cblocks, CB, 0, st>>>(d_slots, n_slots, min_lh, min_obs, scr.block_counts);
+    scan_kernel<<<1, 1024, 0, st>>>(scr.block_counts, cblocks, scr.d_count);
+    uint32_t h_count = 0;
+    KB_CUDA(cudaMemcpyAsync(&h_count, scr.d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    KB_CUDA(cudaStreamSynchronize(st));
+    KB_CUDA(cudaGetLastError());
+    *n_out = h_count;
+    return 2;
+}
+
+int filter_finish(const Slot *d_slots, uint64_t n_slots, uint64_t n_keep, int K, int sw, int x0, int y0, float min_lh,
+                  int min_obs, const float *d_vx, const float *d_vy, ResultScratch &scr, kb_trajectory *d_out,
+                  bool *invalid, cudaStream_t st) {
+    *invalid = false;
+    if (n_keep == 0) return 0;
+    int launches = 0;
+    const uint64_t cblocks = (n_slots + C_TILE - 1) / C_TILE;
+    ensure_scratch(scr, n_keep, cblocks);
+    compact_kernel<<<(unsigned)cblocks, CB, 0, st>>>(d_slots, n_slots, min_lh, min_obs, scr.block_counts,
+                                                     scr.keys[0], scr.vals[0]);
+    launches += 1;
+    launches += radix_sort_pairs(scr, n_keep, st);
+    KB_CUDA(cudaMemsetAsync(scr.d_flag, 0, sizeof(uint32_t), st));
+    gather_kernel<<<(unsigned)((n_keep + 255) / 256), 256, 0, st>>>(d_slots, scr.vals[0], n_keep, K, sw, x0, y0,
+                                                                    d_vx, d_vy, d_out, scr.d_flag);
+    launches += 1;
+    uint32_t h_flag = 0;
+    KB_CUDA(cudaMemcpyAsync(&h_flag, scr.d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    KB_CUDA(cudaStreamSynchronize(st));
+    KB_CUDA(cudaGetLastError());
+    *invalid = h_flag != 0;
+    return launches;
+}
+
+int slots_to_trajectories(const Slot *d_slots, uint64_t n_slots, int K, int sw, int x0, int y0, const float *d_vx,
+                          const float *d_vy, kb_trajectory *d_out, cudaStream_t st) {
+    if (n_slots == 0) return 0;
+    gather_kernel<<<(unsigned)((n_slots + 255) / 256), 256, 0, st>>>(d_slots, nullptr, n_slots, K, sw, x0, y0, d_vx,
+                                                                     d_vy, d_out, nullptr);
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
+// ---- sort an existing trajectory list by lh descending (multi-GPU merge) --------------------------------
+__global__ void traj_keys_kernel(const kb_trajectory *__restrict__ list, uint64_t n, uint32_t *keys, uint32_t *vals) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = lh_key(list[i].lh);
+    vals[i] = (uint32_t)i;
+}
+__global__ void traj_permute_kernel(const kb_trajectory *__restrict__ in, const uint32_t *__restrict__ order,
+                                    uint64_t n, kb_trajectory *__restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = in[order[i]];
+}
+
+int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &scr, kb_trajectory *d_tmp,
+                            cudaStream_t st) {
+    if (n <= 1) return 0;
+    if (n >= (1ull << 32)) throw Error("Too many results for 32-bit indices.");
+    ensure_scratch(scr, n, 1);
+    const unsigned gs = (unsigned)((n + 255) / 256);
+    traj_keys_kernel<<<gs, 256, 0, st>>>(d_list, n, scr.keys[0], scr.vals[0]);
+    int launches = 1 + radix_sort_pairs(scr, n, st);
+    traj_permute_kernel<<<gs, 256, 0, st>>>(d_list, scr.vals[0], n, d_tmp);
+    KB_CUDA(cudaMemcpyAsync(d_list, d_tmp, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToDevice, st));
+    KB_CUDA(cudaGetLastError());
+    return launches + 1;
+}
+
+}  // namespace kb
