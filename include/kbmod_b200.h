@@ -140,6 +140,13 @@ KB_EXPORT int kb_psi_phi_curves(kb_handle h, const kb_trajectory *trjs, uint64_t
 KB_EXPORT int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl1, float coeff, float width,
                                int *idx_out, int *n_kept);
 
+/* ---- measurement hooks (no reference counterpart) ---------------------------------------------------- */
+/* CUDA events recorded on the handle's own stream, so a caller can time a region of calls on the device:
+ * kb_timer_start records the start event; kb_timer_stop records the stop event, waits for it and returns the
+ * elapsed milliseconds between the two. */
+KB_EXPORT int kb_timer_start(kb_handle h);
+KB_EXPORT int kb_timer_stop(kb_handle h, float *ms);
+
 /* ---- multi-GPU merge (no reference counterpart: the reference is single-GPU) ---------------------- */
 /* One process per GPU.  Rank 0 calls kb_nccl_unique_id and ships the 128 bytes to the other ranks by any
  * means; every rank then calls kb_nccl_init.  kb_search_merge_topn all-gathers every rank's sorted results

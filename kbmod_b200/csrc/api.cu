@@ -78,6 +78,7 @@ struct kb_stack_s {
     uint64_t n_results = 0;
     ResultScratch scratch;
     kb_timing timing{};
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
 };
 
 static size_t pair_bytes(int nb) { return 2 * (size_t)nb; }
@@ -219,6 +220,8 @@ static void destroy_handle(kb_handle h) {
         if (h->host_pinned) cudaFreeHost(h->host_array); else free(h->host_array);
     }
     result_scratch_free(h->scratch);
+    if (h->ev_start) cudaEventDestroy(h->ev_start);
+    if (h->ev_stop) cudaEventDestroy(h->ev_stop);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -610,6 +613,28 @@ int kb_clear_results(kb_handle h) {
 int kb_get_timing(kb_handle h, kb_timing *t) {
     KB_API_BEGIN
     *t = h->timing;
+    KB_API_END
+}
+
+int kb_timer_start(kb_handle h) {
+    KB_API_BEGIN
+    use_device(h);
+    if (!h->ev_start) {
+        KB_CUDA(cudaEventCreate(&h->ev_start));
+        KB_CUDA(cudaEventCreate(&h->ev_stop));
+    }
+    KB_CUDA(cudaStreamSynchronize(h->stream));
+    KB_CUDA(cudaEventRecord(h->ev_start, h->stream));
+    KB_API_END
+}
+
+int kb_timer_stop(kb_handle h, float *ms) {
+    KB_API_BEGIN
+    use_device(h);
+    if (!h->ev_start) throw Error("kb_timer_start has not been called.");
+    KB_CUDA(cudaEventRecord(h->ev_stop, h->stream));
+    KB_CUDA(cudaEventSynchronize(h->ev_stop));
+    KB_CUDA(cudaEventElapsedTime(ms, h->ev_start, h->ev_stop));
     KB_API_END
 }
 

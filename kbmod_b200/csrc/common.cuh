@@ -11,6 +11,10 @@
 
 namespace kb {
 
+// The reference's NO_DATA is C's NAN (common.h:34): quiet NaN 0x7fc00000.  Use the same bit pattern so float
+// stacks are memcmp-equal (CUDART_NAN_F is 0x7fffffff).
+#define KB_NAN_F __int_as_float(0x7fc00000)
+
 // ---- error plumbing -------------------------------------------------------------------------------
 void set_error(const std::string &msg);
 

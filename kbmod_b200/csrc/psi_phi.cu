@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
     }
     for (int i = tid; i < tw * th; i += CT_X * CT_Y) {
         const int yy = y0 + i / tw, xx = x0 + i % tw;
-        float a = CUDART_NAN_F, b = CUDART_NAN_F;  // out-of-image taps are skipped == treated as invalid
+        float a = KB_NAN_F, b = KB_NAN_F;  // out-of-image taps are skipped == treated as invalid
         if (xx >= 0 && xx < W && yy >= 0 && yy < H) {
             const size_t g = (size_t)yy * W + xx;
             if (MODE == 0) {
@@ -46,8 +46,8 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
             } else {
                 const float s = in0[g], v = in1[g];
                 const bool vok = isfinite(v) && v != 0.0f;
-                a = (vok && isfinite(s)) ? __fdiv_rn(s, v) : CUDART_NAN_F;   // image_utils_cpp.cpp:142-149
-                b = vok ? __fdiv_rn(1.0f, v) : CUDART_NAN_F;                // :166-171 (double div == f32 div)
+                a = (vok && isfinite(s)) ? __fdiv_rn(s, v) : KB_NAN_F;   // image_utils_cpp.cpp:142-149
+                b = vok ? __fdiv_rn(1.0f, v) : KB_NAN_F;                // :166-171 (double div == f32 div)
             }
         }
         s_a[i] = a;
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
                     }
                 }
             }
-            ra = (portion == 0.0f) ? CUDART_NAN_F : __fdiv_rn(__fmul_rn(sum, psf_total), portion);
+            ra = (portion == 0.0f) ? KB_NAN_F : __fdiv_rn(__fmul_rn(sum, psf_total), portion);
         }
     }
     if (MODE == 1) {
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
                     }
                 }
             }
-            rb = (portion == 0.0f) ? CUDART_NAN_F : __fdiv_rn(__fmul_rn(sum, psf2_total), portion);
+            rb = (portion == 0.0f) ? KB_NAN_F : __fdiv_rn(__fmul_rn(sum, psf2_total), portion);
         }
     }
     const size_t g = (size_t)y * W + x;
@@ -254,7 +254,7 @@ template <typename T2>
 __device__ __forceinline__ T2 canon(T2 v);
 template <>
 __device__ __forceinline__ float2 canon(float2 v) {
-    return (isfinite(v.x) && isfinite(v.y)) ? v : make_float2(CUDART_NAN_F, CUDART_NAN_F);
+    return (isfinite(v.x) && isfinite(v.y)) ? v : make_float2(KB_NAN_F, KB_NAN_F);
 }
 template <>
 __device__ __forceinline__ ushort2 canon(ushort2 v) {
@@ -268,7 +268,7 @@ __device__ __forceinline__ uchar2 canon(uchar2 v) {
 template <typename T2>
 __device__ __forceinline__ T2 invalid_pair();
 template <>
-__device__ __forceinline__ float2 invalid_pair<float2>() { return make_float2(CUDART_NAN_F, CUDART_NAN_F); }
+__device__ __forceinline__ float2 invalid_pair<float2>() { return make_float2(KB_NAN_F, KB_NAN_F); }
 template <>
 __device__ __forceinline__ ushort2 invalid_pair<ushort2>() { return make_ushort2(0, 0); }
 template <>

@@ -21,7 +21,7 @@ __device__ __forceinline__ int predict_index(int pos0, float vel0, double time) 
 
 // kernels.cu:58-68 decode of one stored value: code 0 -> NaN, else (code-1)*scale+min in fp64 -> f32.
 __device__ __forceinline__ float decode_code(unsigned code, float scale, float mn) {
-    if (code == 0u) return CUDART_NAN_F;
+    if (code == 0u) return KB_NAN_F;
     const double v = __dadd_rn(__dmul_rn((double)code - 1.0, (double)scale), (double)mn);
     return (float)v;
 }

@@ -213,7 +213,7 @@ __global__ void curves_kernel(const void *data, const double *times, int T, int 
     const float xp = (float)__dadd_rn(__dadd_rn((double)tr.x, __dmul_rn(tm, (double)tr.vx)), 0.5);
     const float yp = (float)__dadd_rn(__dadd_rn((double)tr.y, __dmul_rn(tm, (double)tr.vy)), 0.5);
     const int col = (int)floorf(xp), row = (int)floorf(yp);
-    float psi = CUDART_NAN_F, phi = CUDART_NAN_F;
+    float psi = KB_NAN_F, phi = KB_NAN_F;
     if (row >= 0 && col >= 0 && row < H && col < W) {
         const size_t idx = 2 * ((size_t)t * H * W + (size_t)row * W + col);
         if (nb == 4) {

@@ -728,6 +728,15 @@ class StackSearch:
         self._log.debug(f"Core search returned {n.value} results after filtering by LH and min_obs.")
         timer.stop()
 
+    def timer_start(self):
+        """Record a CUDA event on the search stream (device-side timing of a region of calls)."""
+        check(lib.kb_timer_start(self._ppa._require()))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        check(lib.kb_timer_stop(self._ppa._require(), C.byref(ms)))
+        return ms.value
+
     def last_timing(self):
         t = KbTiming()
         check(lib.kb_get_timing(self._ppa._require(), C.byref(t)))
