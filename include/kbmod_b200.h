@@ -73,6 +73,9 @@ KB_EXPORT const char *kb_version(void);
 /* kernel_helpers.cpp:23-29 has_gpu() / kernels/kernel_memory.cu:15-60 */
 KB_EXPORT int kb_device_count(int *count);
 KB_EXPORT int kb_gpu_memory(size_t *free_bytes, size_t *total_bytes);
+/* Select the CUDA device for handles created afterwards by this thread (the reference always uses the current
+ * device and never sets it: kernels/kernel_memory.cu; one process per GPU needs this). */
+KB_EXPORT int kb_set_device(int device);
 
 /* ---- image operations (image_utils_cpp.cpp) ------------------------------------------------------ */
 /* convolve_image_gpu (:70-101) with the arithmetic of convolve_image_cpu (:20-68): mask-aware correlation,

@@ -284,6 +284,12 @@ int kb_gpu_memory(size_t *free_bytes, size_t *total_bytes) {
     KB_API_END
 }
 
+int kb_set_device(int device) {
+    KB_API_BEGIN
+    KB_CUDA(cudaSetDevice(device));
+    KB_API_END
+}
+
 static float host_sum(const float *k, int n) {
     float s = 0.0f;
     for (int i = 0; i < n; ++i) s += k[i];  // image_utils_cpp.cpp:30-35 row-major float adds

@@ -1,15 +1,587 @@
-// search_tiled.cu -- placeholder until the TMA-staged kernel lands: always defers to the generic kernel.
-#include "common.cuh"
+// search_tiled.cu -- the throughput path of the search: a TMA-staged, time-tiled gather-reduce kernel.
+//
+// Decomposition (B200-first, not the reference's one-thread-per-pixel serial loop):
+//   * A CTA owns a tile of 32 x BY start pixels (one consumer warp per row, lanes along x) and visits the
+//     candidate list in *groups* of G candidates that are neighbours in velocity space.  Every consumer thread
+//     keeps the G running (psi_sum, phi_sum, count) triples in registers.
+//   * For a group g and an image t, all G trajectories of all tile pixels land inside one small box of the
+//     image: origin (tile + min offset), size (32 + spread_x) x (BY + spread_y).  A dedicated producer warp
+//     fetches those boxes with TMA (cp.async.bulk.tensor, 3-D map over [t][y][x-pairs]) into a ring of shared
+//     memory stages, several images per stage, signalling mbarriers.  Out-of-image parts of a box are filled by
+//     the TMA unit with NaN (float) / 0 (codes) -- exactly the reference's "outside the image = no data".
+//   * Consumers wait on the stage's mbarrier and gather from shared memory: lane l of row r reads the pair at
+//     (r + dy_j(t), l + dx_j(t)) -- x-adjacent lanes read adjacent pairs, so every 64-bit LDS is conflict-free.
+//     The per-(candidate, image) integer offsets dx, dy come from a table built on the host with the
+//     reference's fp64 arithmetic; the table arrives in the same stage by a 1-D bulk copy.
+//   * After the last image of a group the G sums are turned into likelihoods.  A cheap conservative test
+//     (MUFU.RSQ estimate against the current threshold) rejects almost everything; survivors take the exact
+//     IEEE path, the rare sigma-G candidates re-gather their observations (search_device.cuh), and winners
+//     enter the per-pixel top-K list held in registers (ordered by lh, then candidate index == the order the
+//     reference's in-order strict-'>' insertion produces).
+//   * Epilogue: the K winners per pixel are re-evaluated exactly to obtain flux and obs_count and written out.
+//
+// Exactness of the offset table: the reference computes ix = floor((x + fl(vx*t)) + 0.5) in fp64 per pixel.
+// With |x|, |vx*t| < 2^22 the two roundings perturb the sum by < 2^-29, so ix = x + floor(fl(vx*t) + 0.5)
+// unless fl(vx*t)+0.5 lies within 2^-27 of an integer without being exactly one.  Candidates with such an
+// image are not tabulated; every thread evaluates them with the exact per-pixel routine instead.
+#include <cuda.h>
+#include <float.h>
+#include <math.h>
+
+#include <limits.h>
+#include <string.h>
+
+#include <algorithm>
+#include <memory>
+#include <numeric>
+
+#include "search_device.cuh"
+
 namespace kb {
-struct TiledPlan {};
-TiledPlan *tiled_plan_create(const StackView &, const kb_params &, const float *, const float *, uint64_t,
-                             cudaStream_t, std::string *why_not) {
-    if (why_not) *why_not = "tiled kernel not built";
-    return nullptr;
+
+static constexpr int TBX = 32;         // tile width  (lanes)
+static constexpr int TBY = 15;         // tile height (consumer warps); +1 producer warp = 512 threads
+static constexpr int TNT = (TBY + 1) * 32;
+static constexpr int TG = 16;          // candidates per group
+static constexpr int TS = 4;           // pipeline stages
+static constexpr int TCH = 4;          // rows per TMA box
+static constexpr int TMAXTC = 8;       // max images per stage
+static constexpr int STAGE_BYTES = 48 * 1024;
+static constexpr int HDR_BYTES = TMAXTC * TG * 4;
+
+struct PlanView {
+    const int4 *gt;       // [n_groups][T]  {ox, oy, nrows, -}
+    const int *offs;      // [n_groups][T][TG] byte offset inside a time slot
+    const int *cand;      // [n_groups][TG]  candidate index or -1
+    const int *stage_tx;  // [n_stages] bytes the stage's mbarrier must see
+    const int *exact;     // candidates evaluated by the exact routine
+    int n_exact, n_groups, chunks, Tc, BW, slot_bytes, max_ch, T;
+};
+
+struct TiledPlan {
+    CUtensorMap tmap;
+    PlanView v{};
+    void *d_block = nullptr;  // one allocation holding all tables
+    size_t smem = 0;
+    int nb = 4, K = 8;
+    bool sigmag = false;
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-int launch_search_tiled(TiledPlan *, const StackView &, const kb_params &, const float *, const float *, Slot *,
-                        cudaStream_t) {
-    throw Error("tiled kernel not built");
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
 }
-void tiled_plan_destroy(TiledPlan *p) { delete p; }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "WAIT_LOOP:\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+            "@p bra DONE;\n\t"
+            "bra WAIT_LOOP;\n\t"
+            "DONE:\n\t}" ::"r"(bar),
+            "r"(parity)
+            : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2,
+                                            uint32_t bar) {
+    asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+            : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+// ---- pair decode from shared memory ---------------------------------------------------------------------
+template <int NB>
+struct PairLoad;
+template <>
+struct PairLoad<4> {
+    static constexpr int kPairBytes = 8;
+    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &, float &psi, float &phi) {
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(psi), "=f"(phi) : "r"(addr));
+        return phi == phi;  // canonical copy: an invalid pair is (NaN, NaN)
+    }
+};
+// Encoded stacks: the host verified (plan creation) that fmaf((float)(code-1), scale, min) reproduces the
+// reference's fp64 decode for every code, so the gather decodes in fp32.
+template <>
+struct PairLoad<2> {
+    static constexpr int kPairBytes = 4;
+    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
+        uint32_t w;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
+        const float a = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)) - 8388609.0f;  // code - 1, exact
+        const float b = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)) - 8388609.0f;
+        psi = fmaf(a, sv.psi_scale, sv.psi_min);
+        phi = fmaf(b, sv.phi_scale, sv.phi_min);
+        return w != 0u;  // canonical copy: an invalid pair is (0, 0)
+    }
+};
+template <>
+struct PairLoad<1> {
+    static constexpr int kPairBytes = 2;
+    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
+        uint16_t h;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(addr));
+        const uint32_t w = h;
+        const float a = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440)) - 8388609.0f;
+        const float b = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7441)) - 8388609.0f;
+        psi = fmaf(a, sv.psi_scale, sv.psi_min);
+        phi = fmaf(b, sv.phi_scale, sv.phi_min);
+        return w != 0u;
+    }
+};
+
+// ---- the kernel -----------------------------------------------------------------------------------------
+template <int NB, bool SIGMAG, int MAXT, int K>
+__global__ void __launch_bounds__(TNT, 1)
+        search_tiled_kernel(const __grid_constant__ CUtensorMap tmap, const PlanView pv, const StackView sv,
+                            const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
+                            Slot *__restrict__ slots) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t *s_stage = smem;                                              // TS * STAGE_BYTES
+    int *s_hdr = reinterpret_cast<int *>(smem + TS * STAGE_BYTES);        // TS * HDR_BYTES
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(smem + TS * (STAGE_BYTES + HDR_BYTES));  // full[TS], empty[TS]
+    double *s_times = reinterpret_cast<double *>(s_bar + 2 * TS);         // T doubles (exact routines)
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar0 = smem_u32(s_bar);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < TS; ++i) {
+            mbar_init(bar0 + 8 * i, 1);           // full: one arrive (producer) + tx bytes
+            mbar_init(bar0 + 8 * (TS + i), TBY);  // empty: one arrive per consumer warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = threadIdx.x; i < sv.T; i += TNT) s_times[i] = sv.times[i];
+    __syncthreads();
+
+    const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
+    const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
+    const int n_stages = pv.n_groups * pv.chunks;
+    constexpr int PB = PairLoad<NB>::kPairBytes;
+    constexpr int XE = (NB == 4) ? 2 : 1;  // tensor-map elements per pixel along x
+
+    if (warp == TBY) {
+        // ===================== producer warp: TMA box loads + offset-table bulk copies =====================
+        for (int s = 0; s < n_stages; ++s) {
+            const int slot = s % TS;
+            const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
+            if (s >= TS) mbar_wait(empty, ((s / TS) - 1) & 1);
+            const int g = s / pv.chunks, t0 = (s % pv.chunks) * pv.Tc;
+            const int nt = min(pv.Tc, pv.T - t0);
+            if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)__ldg(pv.stage_tx + s));
+            __syncwarp();
+            const uint32_t stage_base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES);
+            for (int i = lane; i < nt * pv.max_ch; i += 32) {
+                const int k = i / pv.max_ch, ch = i % pv.max_ch;
+                const int4 d = __ldg(pv.gt + (size_t)g * pv.T + t0 + k);
+                if (ch * TCH < d.z)
+                    tma_load_3d(stage_base + k * pv.slot_bytes + ch * TCH * pv.BW * PB, &tmap, XE * (tile_x0 + d.x),
+                                tile_y0 + d.y + ch * TCH, t0 + k, full);
+            }
+            if (lane == 0)
+                bulk_load(smem_u32(s_hdr + slot * (HDR_BYTES / 4)), pv.offs + ((size_t)g * pv.T + t0) * TG,
+                          (uint32_t)(nt * TG * 4), full);
+        }
+    } else {
+        // ===================== consumer warps: gather, reduce, rank ========================================
+        const int px = tile_x0 + lane, py = tile_y0 + warp;
+        const uint32_t thread_off = (uint32_t)((warp * pv.BW + lane) * PB);
+        float psi[TG], phi[TG];
+        int cnt[TG];
+        TopK<K> top;
+        top.init();
+#pragma unroll
+        for (int j = 0; j < TG; ++j) {
+            psi[j] = 0.0f;
+            phi[j] = 0.0f;
+            cnt[j] = 0;
+        }
+        for (int s = 0; s < n_stages; ++s) {
+            const int slot = s % TS;
+            const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
+            mbar_wait(full, (s / TS) & 1);
+            const int chunk = s % pv.chunks;
+            const int nt = min(pv.Tc, pv.T - chunk * pv.Tc);
+            const uint32_t base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES) + thread_off;
+            const int4 *hdr = reinterpret_cast<const int4 *>(s_hdr + slot * (HDR_BYTES / 4));
+            for (int k = 0; k < nt; ++k) {
+                const uint32_t bk = base + k * pv.slot_bytes;
+#pragma unroll
+                for (int j4 = 0; j4 < TG / 4; ++j4) {
+                    const int4 o = hdr[k * (TG / 4) + j4];
+                    const int off[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int j = j4 * 4 + q;
+                        float a, b;
+                        if (PairLoad<NB>::load(bk + off[q], sv, a, b)) {
+                            psi[j] = __fadd_rn(psi[j], a);
+                            phi[j] = __fadd_rn(phi[j], b);
+                            cnt[j] += 1;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty);
+            if (chunk == pv.chunks - 1) {
+                // ---- all images of this group are in: turn sums into ranked candidates -------------------
+                const int g = s / pv.chunks;
+#pragma unroll
+                for (int j = 0; j < TG; ++j) {
+                    const int c = __ldg(pv.cand + g * TG + j);
+                    const float ps = psi[j], ph = phi[j];
+                    const int seen = cnt[j];
+                    psi[j] = 0.0f;
+                    phi[j] = 0.0f;
+                    cnt[j] = 0;
+                    if (c < 0 || seen < p.min_observations) continue;  // kernels.cu:318 obs_count < min_obs
+                    // Conservative reject: est approximates lh to ~1e-6 relative; anything clearly below the
+                    // bar (min_lh when sigma-G is on, else the current K-th best) cannot matter.
+                    const float bar_lh = SIGMAG ? p.min_lh : top.worst();
+                    const float est = (ph > 0.0f) ? ps * rsqrtf(ph) : -1.0f;
+                    if (est < bar_lh - (fabsf(est) + fabsf(bar_lh)) * 2e-6f - 1e-30f) continue;
+                    float lh, flux;
+                    finish_sums(ps, ph, lh, flux);
+                    if (SIGMAG) {
+                        if (lh < p.min_lh) continue;  // kernels.cu:201-203 then :319
+                        if (seen != 0) {
+                            sigmag_recompute<NB, MAXT>(sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c), p.sgl_L,
+                                                       p.sgl_H, p.sigmag_coeff, lh, flux, nullptr);
+                            if (lh < p.min_lh) continue;
+                        }
+                    }
+                    if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
+                }
+            }
+        }
+        // ---- candidates whose offsets could not be tabulated exactly: full per-pixel arithmetic ----------
+        for (int e = 0; e < pv.n_exact; ++e) {
+            const int c = __ldg(pv.exact + e);
+            float lh, flux;
+            int obs;
+            evaluate_exact<NB, SIGMAG, MAXT>(sv, s_times, p, px, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux, obs,
+                                             nullptr);
+            if (obs < p.min_observations || (SIGMAG && lh < p.min_lh)) continue;
+            if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
+        }
+        // ---- epilogue: flux and obs_count of the winners, written in the reference's slot order ------------
+        const int xi = px - p.x_start_min, yi = py - p.y_start_min;
+        if (xi < sw && yi < sh) {
+            Slot *my = slots + ((size_t)yi * sw + xi) * p.results_per_pixel;
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                if (r >= (int)p.results_per_pixel) break;
+                Slot out{-FLT_MAX, 0.0f, 0, -1};
+                const int c = top.cand[r];
+                if (c >= 0) {
+                    float lh, flux;
+                    int obs;
+                    evaluate_exact<NB, SIGMAG, MAXT>(sv, s_times, p, px, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux,
+                                                     obs, nullptr);
+                    out = Slot{lh, flux, obs, c};
+                }
+                my[r] = out;
+            }
+        }
+    }
+}
+
+// ---- host: plan construction -------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        KB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres));
+        if (!sym || qres != cudaDriverEntryPointSuccess) throw Error("cuTensorMapEncodeTiled is not available");
+        fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// floor(fl(fl(v*t) + 0.5)) plus the "cannot be tabulated" test described in the file header.
+static inline bool tab_offset(float v, double t, int &off) {
+    const double prod = (double)v * t;
+    if (!(fabs(prod) < 4194304.0)) {
+        off = 0;
+        return false;
+    }
+    const double q = prod + 0.5;
+    const double fl = floor(q);
+    off = (int)fl;
+    const double r = q - fl;
+    const double dist = (r < 0.5) ? r : 1.0 - r;
+    if (dist > 7.450580596923828e-09) return true;          // 2^-27
+    return r == 0.0 && (q - 0.5) == prod;                   // exactly on a boundary: no rounding anywhere
+}
+
+static bool decode_is_exact_in_fp32(int nb, float scale, float mn) {
+    const unsigned n = (nb == 1) ? 255u : 65535u;
+    for (unsigned code = 1; code <= n; ++code) {
+        const float ref = (float)(((double)(float)code - 1.0) * (double)scale + (double)mn);
+        const float fast = fmaf((float)(code - 1), scale, mn);
+        if (memcmp(&ref, &fast, 4) != 0) return false;
+    }
+    return true;
+}
+
+TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not) {
+    auto no = [&](const char *why) -> TiledPlan * {
+        if (why_not) *why_not = why;
+        return nullptr;
+    };
+    const int T = sv.T, K = (int)p.results_per_pixel;
+    if (K > kMaxRegK) return no("results_per_pixel > 8");
+    if (n_cand == 0) return no("no candidates");
+    if (p.do_sigmag_filter && T > kMaxTSigma) return no("too many images for sigma-G");
+    if (sizeof(double) * (size_t)T > 16 * 1024) return no("too many images for the tiled kernel's time table");
+    if (sv.nb != 4) {
+        if (!decode_is_exact_in_fp32(sv.nb, sv.psi_scale, sv.psi_min) ||
+            !decode_is_exact_in_fp32(sv.nb, sv.phi_scale, sv.phi_min))
+            return no("fp32 decode would not be bit-exact for this scale/offset");
+    }
+    std::vector<double> times(T);
+    KB_CUDA(cudaMemcpyAsync(times.data(), sv.times, sizeof(double) * T, cudaMemcpyDeviceToHost, st));
+    KB_CUDA(cudaStreamSynchronize(st));
+    double tabs = 0.0;
+    for (double t : times) {
+        if (!std::isfinite(t)) return no("non-finite time");
+        tabs = std::max(tabs, fabs(t));
+    }
+    const int PB = 2 * sv.nb;
+    const int bw_limit = (sv.nb == 4) ? 128 : 256;  // TMA box: at most 256 elements along x
+
+    // ---- order candidates so that neighbours in the list are neighbours in velocity space -------------------
+    const int N = (int)n_cand;
+    float vx0 = h_vx[0], vx1 = h_vx[0], vy0 = h_vy[0], vy1 = h_vy[0];
+    for (int i = 1; i < N; ++i) {
+        vx0 = std::min(vx0, h_vx[i]); vx1 = std::max(vx1, h_vx[i]);
+        vy0 = std::min(vy0, h_vy[i]); vy1 = std::max(vy1, h_vy[i]);
+    }
+    const double area = std::max((double)(vx1 - vx0), 1e-9) * std::max((double)(vy1 - vy0), 1e-9);
+    const double side = sqrt(area * TG / (double)N);      // velocity-space side of a square holding ~TG candidates
+    const double band_h = std::max(side, 1e-9);
+    std::vector<int> order(N), band(N);
+    for (int i = 0; i < N; ++i) band[i] = (int)std::min(((double)h_vy[i] - vy0) / band_h, 2.0e9);
+    std::iota(order.begin(), order.end(), 0);
+    std::sort(order.begin(), order.end(), [&](int a, int b) {
+        if (band[a] != band[b]) return band[a] < band[b];
+        if (h_vx[a] != h_vx[b]) return (band[a] & 1) ? h_vx[a] > h_vx[b] : h_vx[a] < h_vx[b];
+        if (h_vy[a] != h_vy[b]) return h_vy[a] < h_vy[b];
+        return a < b;
+    });
+    // ---- cut the ordered list into groups whose box stays small (conservative spread from velocities) --------
+    const int sx_lim = std::min(bw_limit - TBX, 96) - 2 - 8, sy_lim = 64;
+    std::vector<int> group_start;  // indices into `order`
+    std::vector<int> exact;
+    std::vector<int> tabulated;
+    tabulated.reserve(N);
+    {
+        // first, weed out candidates that cannot be tabulated
+        for (int oi = 0; oi < N; ++oi) {
+            const int c = order[oi];
+            bool ok = true;
+            for (int t = 0; t < T && ok; ++t) {
+                int o;
+                ok = tab_offset(h_vx[c], times[t], o) && tab_offset(h_vy[c], times[t], o);
+            }
+            (ok ? tabulated : exact).push_back(c);
+        }
+    }
+    const int NTab = (int)tabulated.size();
+    int max_sx = 0, max_sy = 0;
+    {
+        int i = 0;
+        while (i < NTab) {
+            group_start.push_back(i);
+            float gx0 = h_vx[tabulated[i]], gx1 = gx0, gy0 = h_vy[tabulated[i]], gy1 = gy0;
+            int n = 1, sx = 0, sy = 0;
+            while (i + n < NTab && n < TG) {
+                const int c = tabulated[i + n];
+                const float nx0 = std::min(gx0, h_vx[c]), nx1 = std::max(gx1, h_vx[c]);
+                const float ny0 = std::min(gy0, h_vy[c]), ny1 = std::max(gy1, h_vy[c]);
+                const int nsx = (int)ceil(((double)nx1 - nx0) * tabs) + 1, nsy = (int)ceil(((double)ny1 - ny0) * tabs) + 1;
+                if (nsx > sx_lim || nsy > sy_lim) break;
+                gx0 = nx0; gx1 = nx1; gy0 = ny0; gy1 = ny1; sx = nsx; sy = nsy;
+                ++n;
+            }
+            max_sx = std::max(max_sx, sx);
+            max_sy = std::max(max_sy, sy);
+            i += n;
+        }
+        group_start.push_back(NTab);
+    }
+    const int n_groups = (int)group_start.size() - 1;
+    if (n_groups == 0 && exact.empty()) return no("no candidates");
+    // TMA needs the box's first byte 16-byte aligned in global memory: the box origin is rounded down to a
+    // multiple of XA pixels (measured on B200: an unaligned inner coordinate raises "illegal instruction").
+    const int XA = 16 / PB;
+    const int bw_round = (sv.nb == 1) ? 16 : 8;  // keeps every TMA destination 128-byte aligned
+    const int BW = (TBX + max_sx + (XA - 1) + bw_round - 1) / bw_round * bw_round;
+    const int rmax = (TBY + max_sy + TCH - 1) / TCH * TCH;
+    const int slot_bytes = rmax * BW * PB;
+    if (BW > bw_limit || slot_bytes > STAGE_BYTES) return no("velocity spread too large for a shared-memory stage");
+    const int Tc = std::max(1, std::min({TMAXTC, STAGE_BYTES / slot_bytes, T}));
+    const int chunks = (T + Tc - 1) / Tc;
+    const int max_ch = rmax / TCH;
+    const long long n_stages = (long long)n_groups * chunks;
+    if (n_stages >= (1ll << 31)) return no("too many stages");
+
+    // ---- tables --------------------------------------------------------------------------------------------
+    const size_t n_gt = (size_t)std::max(n_groups, 1) * T;
+    std::vector<int4> gt(n_gt);
+    std::vector<int> offs(n_gt * TG, 0), cand((size_t)std::max(n_groups, 1) * TG, -1), stage_tx((size_t)std::max<long long>(n_stages, 1));
+    bool overflow = false;
+#pragma omp parallel for schedule(dynamic, 16)
+    for (int g = 0; g < n_groups; ++g) {
+        const int b = group_start[g], n = group_start[g + 1] - b;
+        int dx[TG], dy[TG];
+        for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
+        for (int t = 0; t < T; ++t) {
+            int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+            for (int j = 0; j < n; ++j) {
+                const int c = tabulated[b + j];
+                tab_offset(h_vx[c], times[t], dx[j]);
+                tab_offset(h_vy[c], times[t], dy[j]);
+                mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
+                mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
+            }
+            const int nrows = TBY + (mxy - mny);
+            mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
+            if (TBX + (mxx - mnx) > BW || nrows > rmax) overflow = true;
+            gt[(size_t)g * T + t] = make_int4(mnx, mny, nrows, 0);
+            int *o = &offs[((size_t)g * T + t) * TG];
+            for (int j = 0; j < TG; ++j)
+                o[j] = (j < n) ? ((dy[j] - mny) * BW + (dx[j] - mnx)) * PB : 0;
+        }
+        for (int ch = 0; ch < chunks; ++ch) {
+            const int t0 = ch * Tc, nt = std::min(Tc, T - t0);
+            int bytes = nt * TG * 4;
+            for (int k = 0; k < nt; ++k)
+                bytes += (gt[(size_t)g * T + t0 + k].z + TCH - 1) / TCH * TCH * BW * PB;
+            stage_tx[(size_t)g * chunks + ch] = bytes;
+        }
+    }
+    if (overflow) return no("internal: box estimate exceeded");
+
+    std::unique_ptr<TiledPlan> plan(new TiledPlan());
+    plan->nb = sv.nb;
+    plan->K = K;
+    plan->sigmag = p.do_sigmag_filter != 0;
+    auto up16 = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t b_gt = up16(gt.size() * sizeof(int4)), b_offs = up16(offs.size() * 4), b_cand = up16(cand.size() * 4),
+                 b_tx = up16(stage_tx.size() * 4), b_ex = up16(std::max<size_t>(exact.size(), 1) * 4);
+    KB_CUDA(cudaMalloc(&plan->d_block, b_gt + b_offs + b_cand + b_tx + b_ex));
+    uint8_t *d = (uint8_t *)plan->d_block;
+    KB_CUDA(cudaMemcpyAsync(d, gt.data(), gt.size() * sizeof(int4), cudaMemcpyHostToDevice, st));
+    KB_CUDA(cudaMemcpyAsync(d + b_gt, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, st));
+    KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs, cand.data(), cand.size() * 4, cudaMemcpyHostToDevice, st));
+    KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs + b_cand, stage_tx.data(), stage_tx.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!exact.empty())
+        KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs + b_cand + b_tx, exact.data(), exact.size() * 4, cudaMemcpyHostToDevice, st));
+    KB_CUDA(cudaStreamSynchronize(st));  // the host vectors die with this scope
+    PlanView &v = plan->v;
+    v.gt = (const int4 *)d;
+    v.offs = (const int *)(d + b_gt);
+    v.cand = (const int *)(d + b_gt + b_offs);
+    v.stage_tx = (const int *)(d + b_gt + b_offs + b_cand);
+    v.exact = (const int *)(d + b_gt + b_offs + b_cand + b_tx);
+    v.n_exact = (int)exact.size();
+    v.n_groups = n_groups;
+    v.chunks = chunks;
+    v.Tc = Tc;
+    v.BW = BW;
+    v.slot_bytes = slot_bytes;
+    v.max_ch = max_ch;
+    v.T = T;
+    plan->smem = (size_t)TS * (STAGE_BYTES + HDR_BYTES) + 2 * TS * 8 + sizeof(double) * (size_t)T;
+
+    // ---- tensor map over the search copy: dims (x elements, rows, images) ----------------------------------------
+    const bool f32 = sv.nb == 4;
+    const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                       : (sv.nb == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16);
+    const cuuint64_t gdim[3] = {(cuuint64_t)(f32 ? 2 * sv.W : sv.W), (cuuint64_t)sv.H, (cuuint64_t)sv.T};
+    const cuuint64_t gstr[2] = {(cuuint64_t)sv.Wp * PB, (cuuint64_t)sv.Wp * PB * sv.H};
+    const cuuint32_t box[3] = {(cuuint32_t)(f32 ? 2 * BW : BW), (cuuint32_t)TCH, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = encode_fn()(&plan->tmap, dt, 3, const_cast<void *>(sv.data), gdim, gstr, box, estr,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                   f32 ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
+                                       : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        cudaFree(plan->d_block);
+        return no("cuTensorMapEncodeTiled failed");
+    }
+    return plan.release();
+}
+
+void tiled_plan_destroy(TiledPlan *plan) {
+    if (!plan) return;
+    if (plan->d_block) cudaFree(plan->d_block);
+    delete plan;
+}
+
+template <int NB, bool SIGMAG, int MAXT>
+static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
+                     Slot *d_slots, dim3 grid, cudaStream_t st) {
+#define KB_LAUNCH_T(KK)                                                                                         \
+    do {                                                                                                        \
+        auto kfn = search_tiled_kernel<NB, SIGMAG, MAXT, KK>;                                                   \
+        KB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan->smem));       \
+        kfn<<<grid, TNT, plan->smem, st>>>(plan->tmap, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
+    } while (0)
+    const int K = plan->K;
+    if (K <= 1) KB_LAUNCH_T(1);
+    else if (K <= 2) KB_LAUNCH_T(2);
+    else if (K <= 4) KB_LAUNCH_T(4);
+    else KB_LAUNCH_T(8);
+#undef KB_LAUNCH_T
+}
+
+template <int NB>
+static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
+                      Slot *d_slots, dim3 grid, cudaStream_t st) {
+    if (!plan->sigmag) launch_k<NB, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 64) launch_k<NB, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 256) launch_k<NB, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else launch_k<NB, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+}
+
+int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
+                        const float *d_vy, Slot *d_slots, cudaStream_t st) {
+    const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
+    dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
+    if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
+    switch (sv.nb) {
+        case 4: launch_nb<4>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 2: launch_nb<2>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 1: launch_nb<1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        default: throw Error("bad num_bytes");
+    }
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
 }  // namespace kb

@@ -1,0 +1,108 @@
+"""Multi-GPU plumbing for the shift-and-stack search: one process per GPU, start pixels sharded in row bands,
+psi/phi replicated, per-GPU sorted results merged by an NCCL all-gather + global sort (in the C library:
+``kb_merge_results_allgather``).  The reference has no multi-GPU code.
+
+torch.distributed is used only as the control plane (rendezvous, barrier, max-reduction of timings and the
+128-byte NCCL unique id); the data path is the library's own NCCL communicator.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._lib import TRAJECTORY_DTYPE, check, lib
+
+
+def env_rank():
+    """(rank, world_size, local_rank) from the torchrun environment (defaults: single process)."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def set_device(local_rank):
+    check(lib.kb_set_device(C.c_int(local_rank)))
+
+
+def row_bands(y_min, y_max, world):
+    """Contiguous start-pixel row bands [y_k, y_{k+1}) covering [y_min, y_max), as even as possible."""
+    n = y_max - y_min
+    edges = [y_min + (n * k) // world for k in range(world + 1)]
+    return [(edges[k], edges[k + 1]) for k in range(world)]
+
+
+def merge_sorted_lists(lists, top_n=0):
+    """Host statement of the merge rule (used by the CPU tests and as documentation of the device merge):
+    concatenate the per-rank lists in rank order and stable-sort by lh descending; keep the first top_n."""
+    cat = np.concatenate([np.asarray(a, dtype=TRAJECTORY_DTYPE) for a in lists]) if lists else np.zeros(0, TRAJECTORY_DTYPE)
+    order = np.argsort(-cat["lh"].astype(np.float64), kind="stable")
+    out = cat[order]
+    return out[:top_n] if top_n else out
+
+
+class Comm:
+    """Control-plane communicator (gloo) + the library's NCCL communicator for the data path."""
+
+    def __init__(self, rank, world, init_nccl=True, backend="gloo"):
+        import torch
+        import torch.distributed as td
+        self.torch, self.td, self.rank, self.world = torch, td, rank, world
+        if not td.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29511")
+            td.init_process_group(backend, rank=rank, world_size=world)
+        self.nccl = False
+        if init_nccl:
+            uid = torch.zeros(128, dtype=torch.uint8)
+            if rank == 0:
+                buf = (C.c_uint8 * 128)()
+                check(lib.kb_nccl_unique_id(buf))
+                uid = torch.tensor(list(buf), dtype=torch.uint8)
+            td.broadcast(uid, src=0)
+            buf = (C.c_uint8 * 128)(*uid.tolist())
+            check(lib.kb_nccl_init(buf, C.c_int(rank), C.c_int(world)))
+            self.nccl = True
+
+    def barrier(self):
+        self.td.barrier()
+
+    def max_float(self, v):
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64)
+        self.td.all_reduce(t, op=self.td.ReduceOp.MAX)
+        return float(t.item())
+
+    def all_gather_arrays(self, arr):
+        """Gather one structured numpy array per rank (control-plane path, used by the CPU tests)."""
+        out = [None] * self.world
+        self.td.all_gather_object(out, np.asarray(arr))
+        return out
+
+    def finalize(self):
+        if self.nccl:
+            check(lib.kb_nccl_finalize())
+            self.nccl = False
+        if self.td.is_initialized():
+            self.td.destroy_process_group()
+
+
+def merge_results(search, top_n=0):
+    """All-gather every rank's sorted result list over NCCL and leave the global best `top_n` (0 = all) as the
+    result list of `search` on every rank.  Returns the merged count."""
+    n = C.c_uint64(0)
+    check(lib.kb_merge_results_allgather(search._ppa._require(), C.c_uint64(top_n), C.byref(n)))
+    return n.value
+
+
+def sharded_search(search, candidates, comm, top_n=0):
+    """search_all over the full start bounds of `search`, sharded in row bands over comm.world ranks."""
+    p = search.params
+    y0, y1 = p.y_start_min, p.y_start_max
+    band = row_bands(y0, y1, comm.world)[comm.rank]
+    try:
+        if band[0] < band[1]:
+            search.set_start_bounds_y(band[0], band[1])
+            search.search_all(candidates, True)
+        else:
+            search.clear_results()
+    finally:
+        p.y_start_min, p.y_start_max = y0, y1
+    return merge_results(search, top_n)

@@ -158,6 +158,18 @@ def eval_trajectory(stack, params, x, y, vx, vy, want_mask=False):
     return res + (mask,) if want_mask else res
 
 
+def eval_many(stack, params, x, y, vx, vy):
+    """Vectorised eval_trajectory: returns (lh, flux, obs) arrays."""
+    x = np.ascontiguousarray(x, dtype=np.int32)
+    y = np.ascontiguousarray(y, dtype=np.int32)
+    vx, vy = _f32(vx), _f32(vy)
+    n = x.size
+    lh, fl, ob = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+    s = stack._c()
+    lib().orc_eval_many(C.byref(s), C.byref(params), C.c_int64(n), _p(x), _p(y), _p(vx), _p(vy), _p(lh), _p(fl), _p(ob))
+    return lh, fl, ob
+
+
 RESULT_DTYPE = np.dtype([("vx", "<f4"), ("vy", "<f4"), ("lh", "<f4"), ("flux", "<f4"), ("x", "<i4"), ("y", "<i4"),
                          ("obs_count", "<i4")])
 

@@ -242,6 +242,13 @@ ORC_API void orc_eval_trajectory(const orc_stack *s, const orc_params *p, int x,
     free(idx);
 }
 
+/* Batch form of orc_eval_trajectory for the tests' record validation. */
+ORC_API void orc_eval_many(const orc_stack *s, const orc_params *p, int64_t n, const int *x, const int *y,
+                           const float *vx, const float *vy, float *lh, float *flux, int *obs) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t i = 0; i < n; ++i) orc_eval_trajectory(s, p, x[i], y[i], vx[i], vy[i], &lh[i], &flux[i], &obs[i], NULL);
+}
+
 /* ---- S2: per-pixel top-K slots, GPU-path semantics (kernels.cu:252-332) ---------------------------- */
 /* Outputs are K*P arrays in slot order ((y_i*sw + x_i)*K + r).  cand_idx = -1 for an empty slot. */
 ORC_API void orc_search_slots(const orc_stack *s, const orc_params *p, const float *vx, const float *vy,
