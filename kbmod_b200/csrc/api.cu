@@ -1,6 +1,7 @@
 // api.cu -- the C-ABI of libkbmod_b200.so (include/kbmod_b200.h): handle management, host orchestration of
 // StackSearch (stack_search.cpp) and PsiPhiArray (psi_phi_array.cpp) on top of the kernels in this directory.
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -534,6 +535,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     if (h->kernel_mode != 1) {
         plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why);
         if (!plan && h->kernel_mode == 2) throw Error("tiled kernel not usable: " + why);
+        if (!plan && getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] generic kernel used: %s\n", why.c_str());
     }
     t_prep.stop(st);
 

@@ -27,6 +27,8 @@
 #include <cuda.h>
 #include <float.h>
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include <limits.h>
 #include <string.h>
@@ -372,72 +374,78 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int PB = 2 * sv.nb;
     const int bw_limit = (sv.nb == 4) ? 128 : 256;  // TMA box: at most 256 elements along x
 
-    // ---- order candidates so that neighbours in the list are neighbours in velocity space -------------------
+    // ---- candidates whose offsets cannot be tabulated exactly go to the exact list ---------------------------------
     const int N = (int)n_cand;
-    float vx0 = h_vx[0], vx1 = h_vx[0], vy0 = h_vy[0], vy1 = h_vy[0];
-    for (int i = 1; i < N; ++i) {
-        vx0 = std::min(vx0, h_vx[i]); vx1 = std::max(vx1, h_vx[i]);
-        vy0 = std::min(vy0, h_vy[i]); vy1 = std::max(vy1, h_vy[i]);
-    }
-    const double area = std::max((double)(vx1 - vx0), 1e-9) * std::max((double)(vy1 - vy0), 1e-9);
-    const double side = sqrt(area * TG / (double)N);      // velocity-space side of a square holding ~TG candidates
-    const double band_h = std::max(side, 1e-9);
-    std::vector<int> order(N), band(N);
-    for (int i = 0; i < N; ++i) band[i] = (int)std::min(((double)h_vy[i] - vy0) / band_h, 2.0e9);
-    std::iota(order.begin(), order.end(), 0);
-    std::sort(order.begin(), order.end(), [&](int a, int b) {
-        if (band[a] != band[b]) return band[a] < band[b];
-        if (h_vx[a] != h_vx[b]) return (band[a] & 1) ? h_vx[a] > h_vx[b] : h_vx[a] < h_vx[b];
-        if (h_vy[a] != h_vy[b]) return h_vy[a] < h_vy[b];
-        return a < b;
-    });
-    // ---- cut the ordered list into groups whose box stays small (conservative spread from velocities) --------
-    const int sx_lim = std::min(bw_limit - TBX, 96) - 2 - 8, sy_lim = 64;
-    std::vector<int> group_start;  // indices into `order`
-    std::vector<int> exact;
-    std::vector<int> tabulated;
+    std::vector<int> exact, tabulated;
     tabulated.reserve(N);
-    {
-        // first, weed out candidates that cannot be tabulated
-        for (int oi = 0; oi < N; ++oi) {
-            const int c = order[oi];
-            bool ok = true;
-            for (int t = 0; t < T && ok; ++t) {
-                int o;
-                ok = tab_offset(h_vx[c], times[t], o) && tab_offset(h_vy[c], times[t], o);
-            }
-            (ok ? tabulated : exact).push_back(c);
+    for (int c = 0; c < N; ++c) {
+        bool ok = true;
+        for (int t = 0; t < T && ok; ++t) {
+            int o;
+            ok = tab_offset(h_vx[c], times[t], o) && tab_offset(h_vy[c], times[t], o);
         }
+        (ok ? tabulated : exact).push_back(c);
     }
     const int NTab = (int)tabulated.size();
+
+    // ---- group the rest: k-d style recursive bisection of velocity space into leaves of <= TG candidates ---------
+    // A group's box is (TBX + sx) x (TBY + sy) pixels with sx, sy ~ velocity extent * max|t|; each cut goes
+    // across the direction that shrinks that box most, at a multiple of TG so the leaves come out full.
+    const int XA = 16 / PB;                          // TMA: box origin must be 16-byte aligned in global memory
+    const int bw_round = (sv.nb == 1) ? 16 : 8;      // keeps every TMA destination 128-byte aligned
+    const int sy_lim = 40;
+    const int rows_lim = (TBY + sy_lim + TCH - 1) / TCH * TCH;
+    const int sx_lim = std::max(8, std::min(STAGE_BYTES / PB / rows_lim, bw_limit) - TBX - XA - bw_round);
+    std::vector<int> group_start;
     int max_sx = 0, max_sy = 0;
     {
-        int i = 0;
-        while (i < NTab) {
-            group_start.push_back(i);
-            float gx0 = h_vx[tabulated[i]], gx1 = gx0, gy0 = h_vy[tabulated[i]], gy1 = gy0;
-            int n = 1, sx = 0, sy = 0;
-            while (i + n < NTab && n < TG) {
-                const int c = tabulated[i + n];
-                const float nx0 = std::min(gx0, h_vx[c]), nx1 = std::max(gx1, h_vx[c]);
-                const float ny0 = std::min(gy0, h_vy[c]), ny1 = std::max(gy1, h_vy[c]);
-                const int nsx = (int)ceil(((double)nx1 - nx0) * tabs) + 1, nsy = (int)ceil(((double)ny1 - ny0) * tabs) + 1;
-                if (nsx > sx_lim || nsy > sy_lim) break;
-                gx0 = nx0; gx1 = nx1; gy0 = ny0; gy1 = ny1; sx = nsx; sy = nsy;
-                ++n;
+        struct Seg { int lo, hi; };
+        std::vector<Seg> stack_;
+        stack_.push_back({0, NTab});
+        std::vector<Seg> leaves;
+        while (!stack_.empty()) {
+            const Seg sg = stack_.back();
+            stack_.pop_back();
+            const int n = sg.hi - sg.lo;
+            if (n <= 0) continue;
+            float x0 = FLT_MAX, x1 = -FLT_MAX, y0 = FLT_MAX, y1 = -FLT_MAX;
+            for (int i = sg.lo; i < sg.hi; ++i) {
+                const int c = tabulated[i];
+                x0 = std::min(x0, h_vx[c]); x1 = std::max(x1, h_vx[c]);
+                y0 = std::min(y0, h_vy[c]); y1 = std::max(y1, h_vy[c]);
             }
-            max_sx = std::max(max_sx, sx);
-            max_sy = std::max(max_sy, sy);
-            i += n;
+            const int sx = (int)ceil(((double)x1 - x0) * tabs) + 1, sy = (int)ceil(((double)y1 - y0) * tabs) + 1;
+            if (n <= TG && sx <= sx_lim && sy <= sy_lim) {
+                leaves.push_back(sg);
+                max_sx = std::max(max_sx, sx);
+                max_sy = std::max(max_sy, sy);
+                continue;
+            }
+            if (n == 1) return no("a single candidate does not fit a stage");
+            // cut across x if that leaves the smaller box, else across y
+            const double ax = (TBX + 0.5 * sx) * (double)(TBY + sy), ay = (TBX + (double)sx) * (TBY + 0.5 * sy);
+            const bool cut_x = (sx > sx_lim) || (!(sy > sy_lim) && ax <= ay);
+            int left = (n > TG) ? ((n / 2 + TG - 1) / TG) * TG : n / 2;
+            if (left >= n) left = n / 2;
+            auto first = tabulated.begin() + sg.lo;
+            if (cut_x)
+                std::nth_element(first, first + left, tabulated.begin() + sg.hi, [&](int a, int b) {
+                    return h_vx[a] != h_vx[b] ? h_vx[a] < h_vx[b] : (h_vy[a] != h_vy[b] ? h_vy[a] < h_vy[b] : a < b);
+                });
+            else
+                std::nth_element(first, first + left, tabulated.begin() + sg.hi, [&](int a, int b) {
+                    return h_vy[a] != h_vy[b] ? h_vy[a] < h_vy[b] : (h_vx[a] != h_vx[b] ? h_vx[a] < h_vx[b] : a < b);
+                });
+            stack_.push_back({sg.lo + left, sg.hi});  // popped second: leaves come out in in-order traversal
+            stack_.push_back({sg.lo, sg.lo + left});
         }
+        for (const Seg &l : leaves) group_start.push_back(l.lo);
         group_start.push_back(NTab);
     }
     const int n_groups = (int)group_start.size() - 1;
     if (n_groups == 0 && exact.empty()) return no("no candidates");
     // TMA needs the box's first byte 16-byte aligned in global memory: the box origin is rounded down to a
     // multiple of XA pixels (measured on B200: an unaligned inner coordinate raises "illegal instruction").
-    const int XA = 16 / PB;
-    const int bw_round = (sv.nb == 1) ? 16 : 8;  // keeps every TMA destination 128-byte aligned
     const int BW = (TBX + max_sx + (XA - 1) + bw_round - 1) / bw_round * bw_round;
     const int rmax = (TBY + max_sy + TCH - 1) / TCH * TCH;
     const int slot_bytes = rmax * BW * PB;
@@ -445,6 +453,10 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int Tc = std::max(1, std::min({TMAXTC, STAGE_BYTES / slot_bytes, T}));
     const int chunks = (T + Tc - 1) / Tc;
     const int max_ch = rmax / TCH;
+    if (getenv("KB_DEBUG"))
+        fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d max_sx=%d max_sy=%d BW=%d rmax=%d "
+                "slot=%d Tc=%d chunks=%d sx_lim=%d sy_lim=%d\n", N, NTab, exact.size(), n_groups, max_sx, max_sy, BW,
+                rmax, slot_bytes, Tc, chunks, sx_lim, sy_lim);
     const long long n_stages = (long long)n_groups * chunks;
     if (n_stages >= (1ll << 31)) return no("too many stages");
 
