@@ -149,6 +149,152 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
     finish_sums(ps, ph, lh, flux);
 }
 
+// Warp-cooperative form of the same sigma-G branch: the 32 lanes of a warp work on ONE (start pixel, candidate)
+// whose parameters are warp-uniform.  Lane l holds observations t = l, l+32, ... (E per lane), so the re-gather
+// is one parallel round of loads; the order statistics come from rank-by-counting over warp shuffles (no sort,
+// no local memory); the kept values are then summed in ascending-lc order exactly like the reference does.
+// The reference's exchange sort leaves equal lc values in a history-dependent order; that order only matters
+// when two tied observations carry different (psi, phi).  In that (rare) case *needs_serial is set and the
+// caller falls back to sigmag_recompute for bit-exactness.  Result is warp-uniform.  T <= 32*E.
+template <int NB, int E>
+__device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
+                                            float vy, float sgl_L, float sgl_H, float coeff, float &lh, float &flux,
+                                            bool &needs_serial) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    float a[E], b[E], lc[E];
+    bool ok[E];
+    unsigned okm[E];
+    int n = 0;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        const int t = e * 32 + lane;
+        a[e] = 0.0f;
+        b[e] = 0.0f;
+        ok[e] = false;
+        if (t < sv.T) {
+            const double tm = times[t];
+            ok[e] = load_pair<NB>(sv, t, predict_index(y, vy, tm), predict_index(x, vx, tm), a[e], b[e]);
+        }
+        lc[e] = (b[e] != 0.0f) ? __fdiv_rn(a[e], b[e]) : 0.0f;
+        okm[e] = __ballot_sync(FULL, ok[e]);
+        n += __popc(okm[e]);
+    }
+    needs_serial = false;
+    if (n == 0) {  // cannot happen behind the caller's gate (seen != 0); keep the reference's degenerate result
+        finish_sums(0.0f, 0.0f, lh, flux);
+        return;
+    }
+    // rank[e] = position of my element in ascending order (ties: earlier image first)
+    int rank[E];
+    bool tie_bad = false;
+#pragma unroll
+    for (int e = 0; e < E; ++e) rank[e] = 0;
+#pragma unroll
+    for (int es = 0; es < E; ++es) {
+        unsigned m = okm[es];
+        while (m) {
+            const int ls = __ffs(m) - 1;
+            m &= m - 1;
+            const float v = __shfl_sync(FULL, lc[es], ls);
+            const float va = __shfl_sync(FULL, a[es], ls);
+            const float vb = __shfl_sync(FULL, b[es], ls);
+            const int ts = es * 32 + ls;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                const int t = e * 32 + lane;
+                const bool eq = (v == lc[e]);
+                if (v < lc[e] || (eq && ts < t)) rank[e] += 1;
+                if (ok[e] && eq && ts != t && (va != a[e] || vb != b[e])) tie_bad = true;
+            }
+        }
+    }
+    if (__any_sync(FULL, tie_bad)) {
+        needs_serial = true;
+        return;
+    }
+    // kernels.cu:94-127 percentile ranks
+    if ((double)sgl_L < 0.0001) sgl_L = (float)0.0001;
+    if ((double)sgl_H > 0.9999) sgl_H = (float)0.9999;
+    int pL = (int)((double)ceilf(__fmul_rn((float)n, sgl_L)) + 0.001) - 1;
+    pL = pL < 0 ? 0 : pL;
+    pL = pL >= n ? n - 1 : pL;
+    int pH = (int)((double)ceilf(__fmul_rn((float)n, sgl_H)) + 0.001) - 1;
+    pH = pH < 0 ? 0 : pH;
+    pH = pH >= n ? n - 1 : pH;
+    int med = (int)(ceil((double)n * 0.5) + 0.001) - 1;
+    med = med < 0 ? 0 : med;
+    med = med >= n ? n - 1 : med;
+    float vL = 0.0f, vH = 0.0f, vM = 0.0f;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        unsigned m = __ballot_sync(FULL, ok[e] && rank[e] == pL);
+        if (m) vL = __shfl_sync(FULL, lc[e], __ffs(m) - 1);
+        m = __ballot_sync(FULL, ok[e] && rank[e] == pH);
+        if (m) vH = __shfl_sync(FULL, lc[e], __ffs(m) - 1);
+        m = __ballot_sync(FULL, ok[e] && rank[e] == med);
+        if (m) vM = __shfl_sync(FULL, lc[e], __ffs(m) - 1);
+    }
+    const float sigma_g = __fmul_rn(coeff, __fsub_rn(vH, vL));
+    const float w = __fmul_rn(2.0f, sigma_g);
+    const float lo = __fsub_rn(vM, w), hi = __fadd_rn(vM, w);
+    // kernels.cu:134-146: first sorted position (below the median) not < lo; last (above the median) still <= hi
+    int n_lo = 0, n_hi = 0;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        n_lo += __popc(__ballot_sync(FULL, ok[e] && rank[e] < med && lc[e] < lo));
+        n_hi += __popc(__ballot_sync(FULL, ok[e] && rank[e] > med && lc[e] <= hi));
+    }
+    const int first = n_lo, last = med + n_hi;
+    float ps = 0.0f, ph = 0.0f;
+    for (int r = first; r <= last; ++r) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            const unsigned m = __ballot_sync(FULL, ok[e] && rank[e] == r);
+            if (m) {
+                const int src = __ffs(m) - 1;
+                ps = __fadd_rn(ps, __shfl_sync(FULL, a[e], src));
+                ph = __fadd_rn(ph, __shfl_sync(FULL, b[e], src));
+            }
+        }
+    }
+    finish_sums(ps, ph, lh, flux);
+}
+
+// Handles every lane of the warp that `need`s the sigma-G recomputation, one lane at a time, cooperatively.
+// (x, y, vx, vy) are the caller's per-lane values; lh/flux are updated for the lanes that needed it.
+// MAXT <= 256 selects the cooperative routine (E = MAXT/32); larger stacks use the serial routine.
+template <int NB, int MAXT>
+__device__ __forceinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
+                                                 float vx, float vy, const kb_params &p, float &lh, float &flux) {
+    if constexpr (MAXT > 256) {
+        if (need) sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux, nullptr);
+        return;
+    } else {
+    constexpr int E = (MAXT + 31) / 32;
+    const int lane = threadIdx.x & 31;
+    unsigned m = __ballot_sync(0xffffffffu, need);
+    while (m) {
+        const int L = __ffs(m) - 1;
+        m &= m - 1;
+        const int bx = __shfl_sync(0xffffffffu, x, L), by = __shfl_sync(0xffffffffu, y, L);
+        const float bvx = __shfl_sync(0xffffffffu, vx, L), bvy = __shfl_sync(0xffffffffu, vy, L);
+        float rl, rf;
+        bool serial;
+        warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, rl, rf, serial);
+        if (lane == L) {
+            if (serial)
+                sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
+                                           nullptr);
+            else {
+                lh = rl;
+                flux = rf;
+            }
+        }
+    }
+    }
+}
+
 // evaluateTrajectory (kernels.cu:154-242), complete: used by the epilogue of the tiled kernel, by the
 // single-trajectory entry point and by the generic kernel.  `times` may point to shared or global memory.
 template <int NB, bool SIGMAG, int MAXT>

@@ -31,6 +31,7 @@
 #include <stdlib.h>
 
 #include <limits.h>
+#include <stddef.h>
 #include <string.h>
 
 #include <algorithm>
@@ -49,19 +50,34 @@ static constexpr int TS = 4;           // pipeline stages
 static constexpr int TCH = 4;          // rows per TMA box
 static constexpr int TMAXTC = 8;       // max images per stage
 static constexpr int STAGE_BYTES = 48 * 1024;
-static constexpr int HDR_BYTES = TMAXTC * TG * 4;
+static constexpr int NMAPS = 16;       // tensor maps with box widths base, base+step, ...
+
+// One pipeline stage as the host lays it out (and as it lands in shared memory by one bulk copy):
+//   meta   {nt | last << 8, group, t0, tx_bytes}
+//   box[k] {ox, oy, nrows | widx << 16, slot_off}   for the nt images of the stage (k < TMAXTC)
+//   offs[k][j] byte offset of candidate j's pixel inside image k's slot, relative to the thread's own pixel
+struct StageRec {
+    int4 meta;
+    int4 box[TMAXTC];
+    int pad[4];
+    int offs[TMAXTC][TG];
+};
+static_assert(sizeof(StageRec) % 16 == 0 && offsetof(StageRec, offs) % 16 == 0, "bulk copies need 16-byte units");
+static constexpr int HDR_BYTES = (sizeof(StageRec) + 127) / 128 * 128;
+
+struct TmapSet {
+    CUtensorMap m[NMAPS];
+};
 
 struct PlanView {
-    const int4 *gt;       // [n_groups][T]  {ox, oy, nrows, -}
-    const int *offs;      // [n_groups][T][TG] byte offset inside a time slot
-    const int *cand;      // [n_groups][TG]  candidate index or -1
-    const int *stage_tx;  // [n_stages] bytes the stage's mbarrier must see
-    const int *exact;     // candidates evaluated by the exact routine
-    int n_exact, n_groups, chunks, Tc, BW, slot_bytes, max_ch, T;
+    const StageRec *stages;  // [n_stages]
+    const int *cand;         // [n_groups][TG]  candidate index or -1
+    const int *exact;        // candidates evaluated by the exact routine
+    int n_exact, n_groups, n_stages, w_base, w_step, max_ch, T;
 };
 
 struct TiledPlan {
-    CUtensorMap tmap;
+    TmapSet maps;
     PlanView v{};
     void *d_block = nullptr;  // one allocation holding all tables
     size_t smem = 0;
@@ -150,12 +166,12 @@ struct PairLoad<1> {
 // ---- the kernel -----------------------------------------------------------------------------------------
 template <int NB, bool SIGMAG, int MAXT, int K>
 __global__ void __launch_bounds__(TNT, 1)
-        search_tiled_kernel(const __grid_constant__ CUtensorMap tmap, const PlanView pv, const StackView sv,
+        search_tiled_kernel(const __grid_constant__ TmapSet maps, const PlanView pv, const StackView sv,
                             const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
                             Slot *__restrict__ slots) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *s_stage = smem;                                              // TS * STAGE_BYTES
-    int *s_hdr = reinterpret_cast<int *>(smem + TS * STAGE_BYTES);        // TS * HDR_BYTES
+    uint8_t *s_hdr = smem + TS * STAGE_BYTES;                             // TS * HDR_BYTES
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(smem + TS * (STAGE_BYTES + HDR_BYTES));  // full[TS], empty[TS]
     double *s_times = reinterpret_cast<double *>(s_bar + 2 * TS);         // T doubles (exact routines)
 
@@ -173,36 +189,38 @@ __global__ void __launch_bounds__(TNT, 1)
 
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
-    const int n_stages = pv.n_groups * pv.chunks;
+    const int n_stages = pv.n_stages;
     constexpr int PB = PairLoad<NB>::kPairBytes;
     constexpr int XE = (NB == 4) ? 2 : 1;  // tensor-map elements per pixel along x
 
     if (warp == TBY) {
-        // ===================== producer warp: TMA box loads + offset-table bulk copies =====================
+        // ===================== producer warp: TMA box loads + the stage record =================================
         for (int s = 0; s < n_stages; ++s) {
             const int slot = s % TS;
             const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
             if (s >= TS) mbar_wait(empty, ((s / TS) - 1) & 1);
-            const int g = s / pv.chunks, t0 = (s % pv.chunks) * pv.Tc;
-            const int nt = min(pv.Tc, pv.T - t0);
-            if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)__ldg(pv.stage_tx + s));
+            const StageRec *rec = pv.stages + s;
+            const int4 meta = __ldg(&rec->meta);
+            const int nt = meta.x & 0xff, t0 = meta.z;
+            if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)meta.w);
             __syncwarp();
             const uint32_t stage_base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES);
             for (int i = lane; i < nt * pv.max_ch; i += 32) {
                 const int k = i / pv.max_ch, ch = i % pv.max_ch;
-                const int4 d = __ldg(pv.gt + (size_t)g * pv.T + t0 + k);
-                if (ch * TCH < d.z)
-                    tma_load_3d(stage_base + k * pv.slot_bytes + ch * TCH * pv.BW * PB, &tmap, XE * (tile_x0 + d.x),
-                                tile_y0 + d.y + ch * TCH, t0 + k, full);
+                const int4 bx = __ldg(&rec->box[k]);
+                const int nrows = bx.z & 0xffff, widx = bx.z >> 16;
+                if (ch * TCH < nrows) {
+                    const int pitch = pv.w_base + pv.w_step * widx;
+                    tma_load_3d(stage_base + bx.w + ch * TCH * pitch * PB, &maps.m[widx], XE * (tile_x0 + bx.x),
+                                tile_y0 + bx.y + ch * TCH, t0 + k, full);
+                }
             }
             if (lane == 0)
-                bulk_load(smem_u32(s_hdr + slot * (HDR_BYTES / 4)), pv.offs + ((size_t)g * pv.T + t0) * TG,
-                          (uint32_t)(nt * TG * 4), full);
+                bulk_load(smem_u32(s_hdr + (size_t)slot * HDR_BYTES), rec, (uint32_t)sizeof(StageRec), full);
         }
     } else {
         // ===================== consumer warps: gather, reduce, rank ========================================
         const int px = tile_x0 + lane, py = tile_y0 + warp;
-        const uint32_t thread_off = (uint32_t)((warp * pv.BW + lane) * PB);
         float psi[TG], phi[TG];
         int cnt[TG];
         TopK<K> top;
@@ -217,15 +235,18 @@ __global__ void __launch_bounds__(TNT, 1)
             const int slot = s % TS;
             const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
             mbar_wait(full, (s / TS) & 1);
-            const int chunk = s % pv.chunks;
-            const int nt = min(pv.Tc, pv.T - chunk * pv.Tc);
-            const uint32_t base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES) + thread_off;
-            const int4 *hdr = reinterpret_cast<const int4 *>(s_hdr + slot * (HDR_BYTES / 4));
+            const StageRec *hdr = reinterpret_cast<const StageRec *>(s_hdr + (size_t)slot * HDR_BYTES);
+            const int4 meta = hdr->meta;
+            const int nt = meta.x & 0xff;
+            const uint32_t base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES);
             for (int k = 0; k < nt; ++k) {
-                const uint32_t bk = base + k * pv.slot_bytes;
+                const int4 bx = hdr->box[k];
+                const int pitch = pv.w_base + pv.w_step * (bx.z >> 16);
+                const uint32_t bk = base + bx.w + (uint32_t)((warp * pitch + lane) * PB);
+                const int4 *ofs = reinterpret_cast<const int4 *>(hdr->offs[k]);
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
-                    const int4 o = hdr[k * (TG / 4) + j4];
+                    const int4 o = ofs[j4];
                     const int off[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
@@ -241,34 +262,36 @@ __global__ void __launch_bounds__(TNT, 1)
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty);
-            if (chunk == pv.chunks - 1) {
+            if (meta.x >> 8) {
                 // ---- all images of this group are in: turn sums into ranked candidates -------------------
-                const int g = s / pv.chunks;
+                const int g = meta.y;
 #pragma unroll
                 for (int j = 0; j < TG; ++j) {
-                    const int c = __ldg(pv.cand + g * TG + j);
+                    const int c = __ldg(pv.cand + g * TG + j);  // warp-uniform
                     const float ps = psi[j], ph = phi[j];
                     const int seen = cnt[j];
                     psi[j] = 0.0f;
                     phi[j] = 0.0f;
                     cnt[j] = 0;
-                    if (c < 0 || seen < p.min_observations) continue;  // kernels.cu:318 obs_count < min_obs
+                    if (c < 0) continue;
+                    bool alive = seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
                     // Conservative reject: est approximates lh to ~1e-6 relative; anything clearly below the
                     // bar (min_lh when sigma-G is on, else the current K-th best) cannot matter.
                     const float bar_lh = SIGMAG ? p.min_lh : top.worst();
                     const float est = (ph > 0.0f) ? ps * rsqrtf(ph) : -1.0f;
-                    if (est < bar_lh - (fabsf(est) + fabsf(bar_lh)) * 2e-6f - 1e-30f) continue;
-                    float lh, flux;
-                    finish_sums(ps, ph, lh, flux);
+                    alive = alive && !(est < bar_lh - (fabsf(est) + fabsf(bar_lh)) * 2e-6f - 1e-30f);
+                    if (!SIGMAG && !alive) continue;
+                    if (SIGMAG && !__any_sync(0xffffffffu, alive)) continue;
+                    float lh = -1.0f, flux = -1.0f;
+                    if (alive) finish_sums(ps, ph, lh, flux);
                     if (SIGMAG) {
-                        if (lh < p.min_lh) continue;  // kernels.cu:201-203 then :319
-                        if (seen != 0) {
-                            sigmag_recompute<NB, MAXT>(sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c), p.sgl_L,
-                                                       p.sgl_H, p.sigmag_coeff, lh, flux, nullptr);
-                            if (lh < p.min_lh) continue;
-                        }
+                        alive = alive && !(lh < p.min_lh);  // kernels.cu:201-203 then :319
+                        const bool need = alive && seen != 0;
+                        sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c), p, lh,
+                                                   flux);
+                        alive = alive && !(lh < p.min_lh);
                     }
-                    if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
+                    if (alive && beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
                 }
             }
         }
@@ -284,22 +307,21 @@ __global__ void __launch_bounds__(TNT, 1)
         }
         // ---- epilogue: flux and obs_count of the winners, written in the reference's slot order ------------
         const int xi = px - p.x_start_min, yi = py - p.y_start_min;
-        if (xi < sw && yi < sh) {
-            Slot *my = slots + ((size_t)yi * sw + xi) * p.results_per_pixel;
 #pragma unroll
-            for (int r = 0; r < K; ++r) {
-                if (r >= (int)p.results_per_pixel) break;
-                Slot out{-FLT_MAX, 0.0f, 0, -1};
-                const int c = top.cand[r];
-                if (c >= 0) {
-                    float lh, flux;
-                    int obs;
-                    evaluate_exact<NB, SIGMAG, MAXT>(sv, s_times, p, px, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux,
-                                                     obs, nullptr);
-                    out = Slot{lh, flux, obs, c};
-                }
-                my[r] = out;
+        for (int r = 0; r < K; ++r) {
+            if (r >= (int)p.results_per_pixel) break;  // warp-uniform
+            Slot out{-FLT_MAX, 0.0f, 0, -1};
+            const int c = top.cand[r];
+            const float vx = (c >= 0) ? __ldg(cvx + c) : 0.0f, vy = (c >= 0) ? __ldg(cvy + c) : 0.0f;
+            float lh = 0.0f, flux = 0.0f;
+            int obs = 0;
+            if (c >= 0) evaluate_exact<NB, false, 1>(sv, s_times, p, px, py, vx, vy, lh, flux, obs, nullptr);
+            if (SIGMAG) {
+                const bool need = c >= 0 && !(obs < p.min_observations || obs == 0 || lh < p.min_lh);
+                sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, vx, vy, p, lh, flux);
             }
+            if (c >= 0) out = Slot{lh, flux, obs, c};
+            if (xi < sw && yi < sh) slots[((size_t)yi * sw + xi) * p.results_per_pixel + r] = out;
         }
     }
 }
@@ -395,7 +417,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int bw_round = (sv.nb == 1) ? 16 : 8;      // keeps every TMA destination 128-byte aligned
     const int sy_lim = 40;
     const int rows_lim = (TBY + sy_lim + TCH - 1) / TCH * TCH;
-    const int sx_lim = std::max(8, std::min(STAGE_BYTES / PB / rows_lim, bw_limit) - TBX - XA - bw_round);
+    const int w_cap = std::min(TBX + bw_round + (NMAPS - 1) * bw_round, bw_limit);  // widest tensor-map box
+    const int sx_lim = std::max(8, std::min(STAGE_BYTES / PB / rows_lim, w_cap) - TBX - XA - bw_round);
     std::vector<int> group_start;
     int max_sx = 0, max_sy = 0;
     {
@@ -444,32 +467,32 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     }
     const int n_groups = (int)group_start.size() - 1;
     if (n_groups == 0 && exact.empty()) return no("no candidates");
-    // TMA needs the box's first byte 16-byte aligned in global memory: the box origin is rounded down to a
-    // multiple of XA pixels (measured on B200: an unaligned inner coordinate raises "illegal instruction").
-    const int BW = (TBX + max_sx + (XA - 1) + bw_round - 1) / bw_round * bw_round;
+    // Box widths come in steps (one tensor map each); a box is as wide as its own (group, image) needs.
+    const int w_step = bw_round, w_base = TBX + w_step;
+    const int w_max = std::min(w_base + (NMAPS - 1) * w_step, bw_limit);
+    if (TBX + max_sx + XA - 1 > w_max) return no("velocity spread too large for the TMA box");
     const int rmax = (TBY + max_sy + TCH - 1) / TCH * TCH;
-    const int slot_bytes = rmax * BW * PB;
-    if (BW > bw_limit || slot_bytes > STAGE_BYTES) return no("velocity spread too large for a shared-memory stage");
-    const int Tc = std::max(1, std::min({TMAXTC, STAGE_BYTES / slot_bytes, T}));
-    const int chunks = (T + Tc - 1) / Tc;
     const int max_ch = rmax / TCH;
-    if (getenv("KB_DEBUG"))
-        fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d max_sx=%d max_sy=%d BW=%d rmax=%d "
-                "slot=%d Tc=%d chunks=%d sx_lim=%d sy_lim=%d\n", N, NTab, exact.size(), n_groups, max_sx, max_sy, BW,
-                rmax, slot_bytes, Tc, chunks, sx_lim, sy_lim);
-    const long long n_stages = (long long)n_groups * chunks;
-    if (n_stages >= (1ll << 31)) return no("too many stages");
 
-    // ---- tables --------------------------------------------------------------------------------------------
-    const size_t n_gt = (size_t)std::max(n_groups, 1) * T;
-    std::vector<int4> gt(n_gt);
-    std::vector<int> offs(n_gt * TG, 0), cand((size_t)std::max(n_groups, 1) * TG, -1), stage_tx((size_t)std::max<long long>(n_stages, 1));
+    // ---- stage records, group by group (greedy packing of consecutive images into <= STAGE_BYTES) ---------------
+    std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
+    std::vector<int> cand((size_t)std::max(n_groups, 1) * TG, -1);
     bool overflow = false;
-#pragma omp parallel for schedule(dynamic, 16)
+#pragma omp parallel for schedule(dynamic, 8)
     for (int g = 0; g < n_groups; ++g) {
         const int b = group_start[g], n = group_start[g + 1] - b;
         int dx[TG], dy[TG];
         for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
+        std::vector<StageRec> &out = per_group[g];
+        StageRec cur;
+        memset(&cur, 0, sizeof(cur));
+        int nt = 0, used = 0, tx = 0, t0 = 0;
+        auto flush = [&](bool last) {
+            cur.meta = make_int4(nt | ((last ? 1 : 0) << 8), g, t0, tx + (int)sizeof(StageRec));
+            out.push_back(cur);
+            memset(&cur, 0, sizeof(cur));
+            nt = used = tx = 0;
+        };
         for (int t = 0; t < T; ++t) {
             int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
             for (int j = 0; j < n; ++j) {
@@ -479,72 +502,93 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
                 mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
                 mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
             }
-            const int nrows = TBY + (mxy - mny);
             mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
-            if (TBX + (mxx - mnx) > BW || nrows > rmax) overflow = true;
-            gt[(size_t)g * T + t] = make_int4(mnx, mny, nrows, 0);
-            int *o = &offs[((size_t)g * T + t) * TG];
+            const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
+            const int widx = std::max(0, (need_w - w_base + w_step - 1) / w_step);
+            const int pitch = w_base + w_step * widx;
+            const int rows_pad = (nrows + TCH - 1) / TCH * TCH;
+            const int bytes = rows_pad * pitch * PB;
+            if (pitch > w_max || widx >= NMAPS || nrows > rmax || bytes > STAGE_BYTES) {
+                overflow = true;
+                break;
+            }
+            if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
+            if (nt == 0) t0 = t;
+            cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 16), used);
             for (int j = 0; j < TG; ++j)
-                o[j] = (j < n) ? ((dy[j] - mny) * BW + (dx[j] - mnx)) * PB : 0;
+                cur.offs[nt][j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
+            used += bytes;
+            tx += bytes;
+            ++nt;
         }
-        for (int ch = 0; ch < chunks; ++ch) {
-            const int t0 = ch * Tc, nt = std::min(Tc, T - t0);
-            int bytes = nt * TG * 4;
-            for (int k = 0; k < nt; ++k)
-                bytes += (gt[(size_t)g * T + t0 + k].z + TCH - 1) / TCH * TCH * BW * PB;
-            stage_tx[(size_t)g * chunks + ch] = bytes;
+        if (nt > 0) flush(true);
+    }
+    if (overflow) return no("velocity spread too large for a shared-memory stage");
+    std::vector<StageRec> stages;
+    {
+        size_t total = 0;
+        for (auto &v : per_group) total += v.size();
+        if (total >= (1ull << 31)) return no("too many stages");
+        stages.reserve(std::max<size_t>(total, 1));
+        for (auto &v : per_group) {
+            stages.insert(stages.end(), v.begin(), v.end());
+            std::vector<StageRec>().swap(v);
         }
     }
-    if (overflow) return no("internal: box estimate exceeded");
+    const int n_stages = (int)stages.size();
+    if (getenv("KB_DEBUG"))
+        fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d stages=%d max_sx=%d max_sy=%d "
+                "w_base=%d w_step=%d rmax=%d sx_lim=%d sy_lim=%d\n", N, NTab, exact.size(), n_groups, n_stages,
+                max_sx, max_sy, w_base, w_step, rmax, sx_lim, sy_lim);
 
     std::unique_ptr<TiledPlan> plan(new TiledPlan());
     plan->nb = sv.nb;
     plan->K = K;
     plan->sigmag = p.do_sigmag_filter != 0;
-    auto up16 = [](size_t b) { return (b + 255) / 256 * 256; };
-    const size_t b_gt = up16(gt.size() * sizeof(int4)), b_offs = up16(offs.size() * 4), b_cand = up16(cand.size() * 4),
-                 b_tx = up16(stage_tx.size() * 4), b_ex = up16(std::max<size_t>(exact.size(), 1) * 4);
-    KB_CUDA(cudaMalloc(&plan->d_block, b_gt + b_offs + b_cand + b_tx + b_ex));
+    auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+    const size_t b_st = up(std::max<size_t>(stages.size(), 1) * sizeof(StageRec)), b_cand = up(cand.size() * 4),
+                 b_ex = up(std::max<size_t>(exact.size(), 1) * 4);
+    KB_CUDA(cudaMalloc(&plan->d_block, b_st + b_cand + b_ex));
     uint8_t *d = (uint8_t *)plan->d_block;
-    KB_CUDA(cudaMemcpyAsync(d, gt.data(), gt.size() * sizeof(int4), cudaMemcpyHostToDevice, st));
-    KB_CUDA(cudaMemcpyAsync(d + b_gt, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, st));
-    KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs, cand.data(), cand.size() * 4, cudaMemcpyHostToDevice, st));
-    KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs + b_cand, stage_tx.data(), stage_tx.size() * 4, cudaMemcpyHostToDevice, st));
+    if (!stages.empty())
+        KB_CUDA(cudaMemcpyAsync(d, stages.data(), stages.size() * sizeof(StageRec), cudaMemcpyHostToDevice, st));
+    KB_CUDA(cudaMemcpyAsync(d + b_st, cand.data(), cand.size() * 4, cudaMemcpyHostToDevice, st));
     if (!exact.empty())
-        KB_CUDA(cudaMemcpyAsync(d + b_gt + b_offs + b_cand + b_tx, exact.data(), exact.size() * 4, cudaMemcpyHostToDevice, st));
+        KB_CUDA(cudaMemcpyAsync(d + b_st + b_cand, exact.data(), exact.size() * 4, cudaMemcpyHostToDevice, st));
     KB_CUDA(cudaStreamSynchronize(st));  // the host vectors die with this scope
     PlanView &v = plan->v;
-    v.gt = (const int4 *)d;
-    v.offs = (const int *)(d + b_gt);
-    v.cand = (const int *)(d + b_gt + b_offs);
-    v.stage_tx = (const int *)(d + b_gt + b_offs + b_cand);
-    v.exact = (const int *)(d + b_gt + b_offs + b_cand + b_tx);
+    v.stages = (const StageRec *)d;
+    v.cand = (const int *)(d + b_st);
+    v.exact = (const int *)(d + b_st + b_cand);
     v.n_exact = (int)exact.size();
     v.n_groups = n_groups;
-    v.chunks = chunks;
-    v.Tc = Tc;
-    v.BW = BW;
-    v.slot_bytes = slot_bytes;
+    v.n_stages = n_stages;
+    v.w_base = w_base;
+    v.w_step = w_step;
     v.max_ch = max_ch;
     v.T = T;
     plan->smem = (size_t)TS * (STAGE_BYTES + HDR_BYTES) + 2 * TS * 8 + sizeof(double) * (size_t)T;
 
-    // ---- tensor map over the search copy: dims (x elements, rows, images) ----------------------------------------
+    // ---- tensor maps over the search copy: dims (x elements, rows, images), one per box width ------------------
     const bool f32 = sv.nb == 4;
     const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                        : (sv.nb == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16);
     const cuuint64_t gdim[3] = {(cuuint64_t)(f32 ? 2 * sv.W : sv.W), (cuuint64_t)sv.H, (cuuint64_t)sv.T};
     const cuuint64_t gstr[2] = {(cuuint64_t)sv.Wp * PB, (cuuint64_t)sv.Wp * PB * sv.H};
-    const cuuint32_t box[3] = {(cuuint32_t)(f32 ? 2 * BW : BW), (cuuint32_t)TCH, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
-    const CUresult r = encode_fn()(&plan->tmap, dt, 3, const_cast<void *>(sv.data), gdim, gstr, box, estr,
-                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                   f32 ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
-                                       : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        cudaFree(plan->d_block);
-        return no("cuTensorMapEncodeTiled failed");
+    for (int i = 0; i < NMAPS; ++i) {
+        const int bw = std::min(w_base + i * w_step, w_max);
+        const cuuint32_t box[3] = {(cuuint32_t)(f32 ? 2 * bw : bw), (cuuint32_t)TCH, 1};
+        const CUresult r = encode_fn()(&plan->maps.m[i], dt, 3, const_cast<void *>(sv.data), gdim, gstr, box, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                       f32 ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
+                                           : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            cudaFree(plan->d_block);
+            plan->d_block = nullptr;
+            return no("cuTensorMapEncodeTiled failed");
+        }
     }
     return plan.release();
 }
@@ -562,7 +606,7 @@ static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, c
     do {                                                                                                        \
         auto kfn = search_tiled_kernel<NB, SIGMAG, MAXT, KK>;                                                   \
         KB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan->smem));       \
-        kfn<<<grid, TNT, plan->smem, st>>>(plan->tmap, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
+        kfn<<<grid, TNT, plan->smem, st>>>(plan->maps, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
     } while (0)
     const int K = plan->K;
     if (K <= 1) KB_LAUNCH_T(1);
@@ -576,6 +620,7 @@ template <int NB>
 static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
     if (!plan->sigmag) launch_k<NB, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 32) launch_k<NB, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
     else if (sv.T <= 64) launch_k<NB, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
     else if (sv.T <= 256) launch_k<NB, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
     else launch_k<NB, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
