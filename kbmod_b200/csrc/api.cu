@@ -68,6 +68,7 @@ struct kb_stack_s {
     void *d_search = nullptr;  // canonical pitched search copy
     double *d_times = nullptr;
     bool on_gpu = false;
+    int zero_marker = 0;  // form of the search copy (StackView::zero_marker)
     int kernel_mode = 0;
     // search state
     DevBuf<float> d_vx, d_vy;
@@ -99,6 +100,7 @@ static StackView make_view(kb_handle h) {
     sv.psi_scale = h->meta.psi_scale;
     sv.phi_min = h->meta.phi_min_val;
     sv.phi_scale = h->meta.phi_scale;
+    sv.zero_marker = h->zero_marker;
     return sv;
 }
 
@@ -237,7 +239,18 @@ static void upload_stack(kb_handle h) {
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
     KB_CUDA(cudaMemcpy2DAsync(h->d_search, (size_t)h->Wp * pb, h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, rows,
                               cudaMemcpyHostToDevice, h->stream));
-    launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->stream);
+    h->zero_marker = 0;
+    const char *nozm = getenv("KB_NO_ZERO_MARKER");
+    if (h->nb == 4 && !(nozm && nozm[0] == '1')) {
+        DevBuf<uint32_t> d_flag;
+        d_flag.ensure(1);
+        launch_detect_valid_zero_pairs(h->d_search, h->Wp, h->T, h->H, h->W, d_flag.p, h->stream);
+        uint32_t flag = 1;
+        KB_CUDA(cudaMemcpyAsync(&flag, d_flag.p, sizeof(flag), cudaMemcpyDeviceToHost, h->stream));
+        KB_CUDA(cudaStreamSynchronize(h->stream));
+        h->zero_marker = flag ? 0 : 1;
+    }
+    launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, h->stream);
     h->on_gpu = true;
 }
 

@@ -54,6 +54,10 @@ struct StackView {
     int T, H, W, Wp;
     int nb;  // bytes per value: 4, 2, 1
     float psi_min, psi_scale, phi_min, phi_scale;
+    // float stacks only: 1 = invalid pairs are stored as (+0, +0) instead of (NaN, NaN).  Adding +0 to a running
+    // float sum is an exact no-op, so the search kernel can accumulate without testing validity.  Chosen at upload
+    // time when no *valid* pair is (0, 0) (upload_stack checks), which keeps "pair is zero" == "pair is invalid".
+    int zero_marker;
 };
 
 // Per-pixel result slot written by the search kernels: 16 bytes, [pixel][K].
@@ -102,7 +106,10 @@ int launch_encode(const float2 *d_pairs, uint64_t n, int nb, const float psi_p[3
                   cudaStream_t st);
 // rows of `src_pitch` pixel pairs -> canonical search copy with pitch Wp (in place when src == dst and pitches match).
 int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
-                        cudaStream_t st);
+                        int zero_marker, cudaStream_t st);
+// float stacks: sets *d_flag to 1 when some valid pair is exactly (0, 0) (then the zero marker cannot be used).
+int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int H, int W, uint32_t *d_flag,
+                                   cudaStream_t st);
 float ordered_to_float(uint32_t u);
 
 // results.cu

@@ -284,11 +284,48 @@ __global__ void canonicalise_kernel(const T2 *src, int src_pitch, T2 *dst, uint6
         dst[i] = (c < W) ? canon(src[r * src_pitch + c]) : invalid_pair<T2>();  // padding columns: invalid
     }
 }
+
+// float stacks, zero-marker form: invalid -> (+0, +0)
+__global__ void canonicalise_zero_kernel(const float2 *src, int src_pitch, float2 *dst, uint64_t rows, int W, int Wp) {
+    const uint64_t total = rows * (uint64_t)Wp;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / Wp;
+        const int c = (int)(i % Wp);
+        float2 v = make_float2(0.0f, 0.0f);
+        if (c < W) {
+            const float2 s = src[r * src_pitch + c];
+            if (isfinite(s.x) && isfinite(s.y)) v = s;
+        }
+        dst[i] = v;
+    }
+}
+
+__global__ void detect_valid_zero_kernel(const float2 *src, int src_pitch, uint64_t rows, int W, uint32_t *flag) {
+    const uint64_t total = rows * (uint64_t)W;
+    bool hit = false;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const float2 s = src[(i / W) * src_pitch + (i % W)];
+        hit |= (s.x == 0.0f && s.y == 0.0f);  // finite by construction
+    }
+    if (__any_sync(0xffffffffu, hit) && (threadIdx.x & 31) == 0) atomicExch(flag, 1u);
+}
+
+int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int H, int W, uint32_t *d_flag,
+                                   cudaStream_t st) {
+    KB_CUDA(cudaMemsetAsync(d_flag, 0, sizeof(uint32_t), st));
+    detect_valid_zero_kernel<<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (uint64_t)T * H, W, d_flag);
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
 int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
-                        cudaStream_t st) {
+                        int zero_marker, cudaStream_t st) {
     if (d_src == d_dst && src_pitch != Wp) throw Error("in-place canonicalise needs equal pitches");
     const uint64_t rows = (uint64_t)T * H;
-    if (nb == 4)
+    if (nb == 4 && zero_marker)
+        canonicalise_zero_kernel<<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, rows, W, Wp);
+    else if (nb == 4)
         canonicalise_kernel<float2><<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, rows, W, Wp);
     else if (nb == 2)
         canonicalise_kernel<ushort2><<<148 * 8, 256, 0, st>>>((const ushort2 *)d_src, src_pitch, (ushort2 *)d_dst, rows, W, Wp);

@@ -35,6 +35,7 @@ __device__ __forceinline__ bool load_pair(const StackView &sv, int t, int iy, in
         const float2 v = __ldg(reinterpret_cast<const float2 *>(sv.data) + idx);
         psi = v.x;
         phi = v.y;
+        if (sv.zero_marker) return ((__float_as_uint(v.x) | __float_as_uint(v.y)) << 1) != 0u;  // (0,0) == invalid
     } else if (NB == 2) {
         const ushort2 v = __ldg(reinterpret_cast<const ushort2 *>(sv.data) + idx);
         psi = decode_code(v.x, sv.psi_scale, sv.psi_min);
@@ -111,7 +112,7 @@ __device__ inline void sigmag_indices(const float *values, int n, float sgl0, fl
 template <int NB, int MAXT>
 __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double *times, int x, int y, float vx,
                                               float vy, float sgl_L, float sgl_H, float coeff, float &lh,
-                                              float &flux, uint8_t *mask) {
+                                              float &flux, uint8_t *mask, int *n_valid = nullptr) {
     float psi_a[MAXT], phi_a[MAXT], lc[MAXT];
     int idx[MAXT];
     int seen = 0;
@@ -128,6 +129,7 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
             ++seen;
         }
     }
+    if (n_valid) *n_valid = seen;
     // Remember the time index of each observation when a keep-mask is wanted.
     uint16_t *tix = nullptr;
     uint16_t tix_store[MAXT];
@@ -158,8 +160,8 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 // caller falls back to sigmag_recompute for bit-exactness.  Result is warp-uniform.  T <= 32*E.
 template <int NB, int E>
 __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
-                                            float vy, float sgl_L, float sgl_H, float coeff, float &lh, float &flux,
-                                            bool &needs_serial) {
+                                            float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float &lh,
+                                            float &flux, int &n_valid, bool &needs_serial) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     float a[E], b[E], lc[E];
@@ -181,10 +183,9 @@ __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *t
         n += __popc(okm[e]);
     }
     needs_serial = false;
-    if (n == 0) {  // cannot happen behind the caller's gate (seen != 0); keep the reference's degenerate result
-        finish_sums(0.0f, 0.0f, lh, flux);
-        return;
-    }
+    n_valid = n;
+    // kernels.cu:201-203: too few observations (or none) -> the clip is skipped; the caller decides what that means
+    if (n < min_obs || n == 0) return;
     // rank[e] = position of my element in ascending order (ties: earlier image first)
     int rank[E];
     bool tie_bad = false;
@@ -262,13 +263,24 @@ __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *t
 }
 
 // Handles every lane of the warp that `need`s the sigma-G recomputation, one lane at a time, cooperatively.
-// (x, y, vx, vy) are the caller's per-lane values; lh/flux are updated for the lanes that needed it.
+// (x, y, vx, vy) are the caller's per-lane values.  For the lanes that needed it: n_valid receives the number of
+// valid observations; lh/flux are replaced by the clipped values when n_valid >= max(min_obs, 1) (otherwise the
+// reference skips the clip, kernels.cu:201-203, and lh/flux are left as they were).
 // MAXT <= 256 selects the cooperative routine (E = MAXT/32); larger stacks use the serial routine.
 template <int NB, int MAXT>
 __device__ __forceinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
-                                                 float vx, float vy, const kb_params &p, float &lh, float &flux) {
+                                                 float vx, float vy, const kb_params &p, float &lh, float &flux,
+                                                 int &n_valid) {
     if constexpr (MAXT > 256) {
-        if (need) sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux, nullptr);
+        if (need) {
+            float l2 = lh, f2 = flux;
+            sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, l2, f2, nullptr,
+                                       &n_valid);
+            if (!(n_valid < p.min_observations || n_valid == 0)) {
+                lh = l2;
+                flux = f2;
+            }
+        }
         return;
     } else {
     constexpr int E = (MAXT + 31) / 32;
@@ -279,14 +291,17 @@ __device__ __forceinline__ void sigmag_for_lanes(bool need, const StackView &sv,
         m &= m - 1;
         const int bx = __shfl_sync(0xffffffffu, x, L), by = __shfl_sync(0xffffffffu, y, L);
         const float bvx = __shfl_sync(0xffffffffu, vx, L), bvy = __shfl_sync(0xffffffffu, vy, L);
-        float rl, rf;
+        float rl = 0.0f, rf = 0.0f;
+        int rn = 0;
         bool serial;
-        warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, rl, rf, serial);
+        warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, p.min_observations, rl, rf,
+                           rn, serial);
         if (lane == L) {
+            n_valid = rn;
             if (serial)
                 sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
                                            nullptr);
-            else {
+            else if (!(rn < p.min_observations || rn == 0)) {
                 lh = rl;
                 flux = rf;
             }
@@ -320,6 +335,19 @@ __device__ __forceinline__ void evaluate_exact(const StackView &sv, const double
         if (!(seen < p.min_observations || seen == 0 || lh < p.min_lh))
             sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux, mask);
     }
+}
+
+// Number of valid observations along one trajectory (the obs_count of kernels.cu:195), by re-gathering.
+template <int NB>
+__device__ __forceinline__ int count_observations(const StackView &sv, const double *times, int x, int y, float vx,
+                                                  float vy) {
+    int seen = 0;
+    for (int t = 0; t < sv.T; ++t) {
+        const double tm = times[t];
+        float a, b;
+        if (load_pair<NB>(sv, t, predict_index(y, vy, tm), predict_index(x, vx, tm), a, b)) ++seen;
+    }
+    return seen;
 }
 
 // Ordering used for the per-pixel list when candidates are not visited in list order: higher lh first; equal lh

@@ -164,7 +164,10 @@ struct PairLoad<1> {
 };
 
 // ---- the kernel -----------------------------------------------------------------------------------------
-template <int NB, bool SIGMAG, int MAXT, int K>
+// ZM (float stacks in zero-marker form, StackView::zero_marker): invalid pairs and out-of-image pixels read as
+// (+0, +0), so the inner loop adds unconditionally and keeps no per-candidate observation count; the count is
+// recovered by re-gathering for the few candidates whose lh reaches the bar.
+template <int NB, bool ZM, bool SIGMAG, int MAXT, int K>
 __global__ void __launch_bounds__(TNT, 1)
         search_tiled_kernel(const __grid_constant__ TmapSet maps, const PlanView pv, const StackView sv,
                             const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
@@ -195,41 +198,53 @@ __global__ void __launch_bounds__(TNT, 1)
 
     if (warp == TBY) {
         // ===================== producer warp: TMA box loads + the stage record =================================
+        // Lane l < 9 keeps int4 #l of the *next* stage record (meta + 8 boxes) in a register, loaded one stage ahead
+        // so the global-memory latency overlaps the wait for a free slot; fields are handed out by shuffles.
+        const unsigned FULLM = 0xffffffffu;
+        auto fetch = [&](int s) -> int4 {
+            if (lane < 1 + TMAXTC && s < n_stages) return __ldg(reinterpret_cast<const int4 *>(pv.stages + s) + lane);
+            return make_int4(0, 0, 0, 0);
+        };
+        int4 nxt = fetch(0);
         for (int s = 0; s < n_stages; ++s) {
             const int slot = s % TS;
             const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
+            const int4 cur = nxt;
+            nxt = fetch(s + 1);
             if (s >= TS) mbar_wait(empty, ((s / TS) - 1) & 1);
-            const StageRec *rec = pv.stages + s;
-            const int4 meta = __ldg(&rec->meta);
-            const int nt = meta.x & 0xff, t0 = meta.z;
-            if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)meta.w);
+            const int nt = __shfl_sync(FULLM, cur.x, 0) & 0xff, t0 = __shfl_sync(FULLM, cur.z, 0);
+            const int tx = __shfl_sync(FULLM, cur.w, 0);
+            if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)tx);
             __syncwarp();
             const uint32_t stage_base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES);
-            for (int i = lane; i < nt * pv.max_ch; i += 32) {
-                const int k = i / pv.max_ch, ch = i % pv.max_ch;
-                const int4 bx = __ldg(&rec->box[k]);
-                const int nrows = bx.z & 0xffff, widx = bx.z >> 16;
-                if (ch * TCH < nrows) {
+            const int total = nt * pv.max_ch;
+            for (int i0 = 0; i0 < total; i0 += 32) {
+                const int i = i0 + lane;
+                const int k = min(i / pv.max_ch, TMAXTC - 1), ch = i % pv.max_ch;
+                const int bxx = __shfl_sync(FULLM, cur.x, k + 1), bxy = __shfl_sync(FULLM, cur.y, k + 1);
+                const int bxz = __shfl_sync(FULLM, cur.z, k + 1), bxw = __shfl_sync(FULLM, cur.w, k + 1);
+                const int nrows = bxz & 0xffff, widx = bxz >> 16;
+                if (i < total && ch * TCH < nrows) {
                     const int pitch = pv.w_base + pv.w_step * widx;
-                    tma_load_3d(stage_base + bx.w + ch * TCH * pitch * PB, &maps.m[widx], XE * (tile_x0 + bx.x),
-                                tile_y0 + bx.y + ch * TCH, t0 + k, full);
+                    tma_load_3d(stage_base + bxw + ch * TCH * pitch * PB, &maps.m[widx], XE * (tile_x0 + bxx),
+                                tile_y0 + bxy + ch * TCH, t0 + k, full);
                 }
             }
             if (lane == 0)
-                bulk_load(smem_u32(s_hdr + (size_t)slot * HDR_BYTES), rec, (uint32_t)sizeof(StageRec), full);
+                bulk_load(smem_u32(s_hdr + (size_t)slot * HDR_BYTES), pv.stages + s, (uint32_t)sizeof(StageRec), full);
         }
     } else {
         // ===================== consumer warps: gather, reduce, rank ========================================
         const int px = tile_x0 + lane, py = tile_y0 + warp;
         float psi[TG], phi[TG];
-        int cnt[TG];
+        int cnt[ZM ? 1 : TG];
         TopK<K> top;
         top.init();
 #pragma unroll
         for (int j = 0; j < TG; ++j) {
             psi[j] = 0.0f;
             phi[j] = 0.0f;
-            cnt[j] = 0;
+            if (!ZM) cnt[j] = 0;
         }
         for (int s = 0; s < n_stages; ++s) {
             const int slot = s % TS;
@@ -252,7 +267,11 @@ __global__ void __launch_bounds__(TNT, 1)
                     for (int q = 0; q < 4; ++q) {
                         const int j = j4 * 4 + q;
                         float a, b;
-                        if (PairLoad<NB>::load(bk + off[q], sv, a, b)) {
+                        const bool ok = PairLoad<NB>::load(bk + off[q], sv, a, b);
+                        if (ZM) {
+                            psi[j] = __fadd_rn(psi[j], a);
+                            phi[j] = __fadd_rn(phi[j], b);
+                        } else if (ok) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
                             cnt[j] += 1;
@@ -269,29 +288,43 @@ __global__ void __launch_bounds__(TNT, 1)
                 for (int j = 0; j < TG; ++j) {
                     const int c = __ldg(pv.cand + g * TG + j);  // warp-uniform
                     const float ps = psi[j], ph = phi[j];
-                    const int seen = cnt[j];
                     psi[j] = 0.0f;
                     phi[j] = 0.0f;
-                    cnt[j] = 0;
+                    int seen = 0;
+                    if (!ZM) {
+                        seen = cnt[j];
+                        cnt[j] = 0;
+                    }
                     if (c < 0) continue;
-                    bool alive = seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
+                    bool alive = ZM || seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
                     // Conservative reject: est approximates lh to ~1e-6 relative; anything clearly below the
                     // bar (min_lh when sigma-G is on, else the current K-th best) cannot matter.
                     const float bar_lh = SIGMAG ? p.min_lh : top.worst();
                     const float est = (ph > 0.0f) ? ps * rsqrtf(ph) : -1.0f;
                     alive = alive && !(est < bar_lh - (fabsf(est) + fabsf(bar_lh)) * 2e-6f - 1e-30f);
-                    if (!SIGMAG && !alive) continue;
-                    if (SIGMAG && !__any_sync(0xffffffffu, alive)) continue;
-                    float lh = -1.0f, flux = -1.0f;
-                    if (alive) finish_sums(ps, ph, lh, flux);
-                    if (SIGMAG) {
+                    if (!SIGMAG) {
+                        if (!alive) continue;
+                        float lh, flux;
+                        finish_sums(ps, ph, lh, flux);
+                        if (!beats(lh, c, top.worst(), top.cand[K - 1])) continue;
+                        if (ZM && p.min_observations > 0 &&
+                            count_observations<NB>(sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c)) <
+                                    p.min_observations)
+                            continue;
+                        top.insert(lh, c);
+                    } else {
+                        if (!__any_sync(0xffffffffu, alive)) continue;
+                        float lh = -1.0f, flux = -1.0f;
+                        if (alive) finish_sums(ps, ph, lh, flux);
                         alive = alive && !(lh < p.min_lh);  // kernels.cu:201-203 then :319
-                        const bool need = alive && seen != 0;
+                        const bool need = alive && (ZM || seen != 0);
+                        int nv = seen;
                         sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c), p, lh,
-                                                   flux);
+                                                   flux, nv);
+                        if (ZM && need && nv < p.min_observations) alive = false;
                         alive = alive && !(lh < p.min_lh);
+                        if (alive && beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
                     }
-                    if (alive && beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
                 }
             }
         }
@@ -318,7 +351,8 @@ __global__ void __launch_bounds__(TNT, 1)
             if (c >= 0) evaluate_exact<NB, false, 1>(sv, s_times, p, px, py, vx, vy, lh, flux, obs, nullptr);
             if (SIGMAG) {
                 const bool need = c >= 0 && !(obs < p.min_observations || obs == 0 || lh < p.min_lh);
-                sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, vx, vy, p, lh, flux);
+                int nv = obs;
+                sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, vx, vy, p, lh, flux, nv);
             }
             if (c >= 0) out = Slot{lh, flux, obs, c};
             if (xi < sw && yi < sh) slots[((size_t)yi * sw + xi) * p.results_per_pixel + r] = out;
@@ -582,8 +616,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
         const CUresult r = encode_fn()(&plan->maps.m[i], dt, 3, const_cast<void *>(sv.data), gdim, gstr, box, estr,
                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                       f32 ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
-                                           : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                                       (f32 && !sv.zero_marker) ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
+                                                                : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
             cudaFree(plan->d_block);
             plan->d_block = nullptr;
@@ -599,12 +633,12 @@ void tiled_plan_destroy(TiledPlan *plan) {
     delete plan;
 }
 
-template <int NB, bool SIGMAG, int MAXT>
+template <int NB, bool ZM, bool SIGMAG, int MAXT>
 static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                      Slot *d_slots, dim3 grid, cudaStream_t st) {
 #define KB_LAUNCH_T(KK)                                                                                         \
     do {                                                                                                        \
-        auto kfn = search_tiled_kernel<NB, SIGMAG, MAXT, KK>;                                                   \
+        auto kfn = search_tiled_kernel<NB, ZM, SIGMAG, MAXT, KK>;                                                   \
         KB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan->smem));       \
         kfn<<<grid, TNT, plan->smem, st>>>(plan->maps, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
     } while (0)
@@ -616,14 +650,14 @@ static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, c
 #undef KB_LAUNCH_T
 }
 
-template <int NB>
+template <int NB, bool ZM>
 static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
-    if (!plan->sigmag) launch_k<NB, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 32) launch_k<NB, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 64) launch_k<NB, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 256) launch_k<NB, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else launch_k<NB, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    if (!plan->sigmag) launch_k<NB, ZM, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 32) launch_k<NB, ZM, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 64) launch_k<NB, ZM, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 256) launch_k<NB, ZM, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else launch_k<NB, ZM, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
@@ -632,9 +666,12 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
     if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
     switch (sv.nb) {
-        case 4: launch_nb<4>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
-        case 2: launch_nb<2>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
-        case 1: launch_nb<1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 4:
+            if (sv.zero_marker) launch_nb<4, true>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+            else launch_nb<4, false>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+            break;
+        case 2: launch_nb<2, false>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 1: launch_nb<1, false>(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
         default: throw Error("bad num_bytes");
     }
     KB_CUDA(cudaGetLastError());
