@@ -30,6 +30,11 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE search-kernel launch from an `ncu --set full` capture of this
+# workload shape (profiles/r01_ncu_search_tiled_raw.csv: 4.628 GB read + 0.713 GB written; the algorithmic gather
+# bytes of the same launch are 1342 GB, the stack itself is 0.671 GB).
+NCU_DRAM_BYTES_PER_LAUNCH = {("C2", True): 5.34e9}
+
 METRIC = "pixel-trajectory-obs evals/sec"
 UNIT = "evals/s"
 
@@ -263,7 +268,8 @@ def run_ours(args, c, cfg_name):
     kernel_ms = k_ms / max(n_kernel, 1)
     achieved = evals_rank * bytes_per_eval / (kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "search_tiled_kernel" if tiled else "search_generic_kernel",
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get((cfg_name, bool(tiled))), "traffic_unit": "bytes/launch",
+                "kernel": "search_tiled_kernel" if tiled else "search_generic_kernel",
                 "kernel_ms": kernel_ms, "bytes_per_eval": bytes_per_eval, "peak_source": peak_src,
                 "note": "algorithmic gather bytes (P*N*T pairs) / kernel time; gathers are served from shared "
                         "memory / L2, so the fraction of the HBM copy peak can exceed 1"}
