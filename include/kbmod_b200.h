@@ -150,6 +150,28 @@ KB_EXPORT int kb_sigmag_filtered_indices(const float *values, int n, float sgl0,
 KB_EXPORT int kb_timer_start(kb_handle h);
 KB_EXPORT int kb_timer_stop(kb_handle h, float *ms);
 
+/* ---- for callers that cannot allocate device memory --------------------------------------------------------
+ * No counterpart in the reference (its sort is a host-side __gnu_parallel::sort, trajectory_list.cpp:96-107).
+ *
+ * Sorts the `n` trajectories at DEVICE address `d_list` in place by lh, highest first, ties keeping their input
+ * order -- the same stable radix sort kb_search uses for its result list -- without a single cudaMalloc/cudaFree.
+ * It exists for two kinds of caller.  Services that give every last byte of HBM to their own memory pool at
+ * start-up and hand this library buffers out of it: a late cudaMalloc simply fails there.  And latency-critical
+ * loops that keep several streams busy: cudaMalloc and cudaFree synchronise the whole device, which stalls
+ * every other stream each time a result list is sorted.
+ *
+ * The sort's working memory is a fixed array that is part of the library image: every GPU that loads
+ * libkbmod_b200.so carries it (about 12 MB) until the process exits.  Consequences:
+ *   - n may be at most KB_STATIC_SORT_MAX; larger lists are refused with an error (nothing is sorted).
+ *   - All calls on a device share that one array.  Calls whose GPU work can overlap (different streams, or
+ *     different host threads) race on it: issue them on one stream, or order them with events.
+ *   - The first call on each device looks up where that device placed the array (cudaGetSymbolAddress).  Make
+ *     that first call during set-up, before any CUDA stream capture begins on the device.
+ * The work is enqueued on `cuda_stream` (a cudaStream_t passed as void*; NULL = the default stream) and the call
+ * returns without waiting for it. */
+#define KB_STATIC_SORT_MAX (1u << 18)
+KB_EXPORT int kb_sort_trajectories_static(kb_trajectory *d_list, uint64_t n, void *cuda_stream);
+
 /* ---- multi-GPU merge (no reference counterpart: the reference is single-GPU) ---------------------- */
 /* One process per GPU.  Rank 0 calls kb_nccl_unique_id and ships the 128 bytes to the other ranks by any
  * means; every rank then calls kb_nccl_init.  kb_search_merge_topn all-gathers every rank's sorted results

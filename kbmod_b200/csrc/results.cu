@@ -364,4 +364,65 @@ int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &sc
     return launches + 1;
 }
 
+// ---- sorting a trajectory list without allocating anything ----------------------------------------------------
+// The scratch the radix sort needs (two key buffers, two index buffers, the digit histograms and a staging copy of
+// the list) lives in one file-scope device array instead of cudaMalloc'd buffers.  Every GPU that loads this
+// library holds the array (about 12 MB) until the process exits.
+static constexpr uint64_t kStaticSortMax = KB_STATIC_SORT_MAX;
+static constexpr uint64_t kStaticHistWords = 256 * ((kStaticSortMax + R_TILE - 1) / R_TILE + 1);
+static constexpr uint64_t kStaticScratchBytes =
+        4 * sizeof(uint32_t) * kStaticSortMax + sizeof(uint32_t) * kStaticHistWords + sizeof(kb_trajectory) * kStaticSortMax;
+static __device__ __align__(256) unsigned char g_static_sort_scratch[kStaticScratchBytes];
+
+// In host code `g_static_sort_scratch` is only a stand-in for the symbol, not a device address: the address each
+// device gave the array is looked up once per device (with that device current) and cached here.
+static unsigned char *g_static_scratch_addr[64] = {nullptr};
+
+static unsigned char *static_scratch_for_current_device() {
+    int dev = -1;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw Error("device ordinal out of range for the static sort scratch");
+    if (!g_static_scratch_addr[dev]) {
+        void *ptr = nullptr;
+        KB_CUDA(cudaGetSymbolAddress(&ptr, g_static_sort_scratch));
+        if (!ptr) throw Error("cudaGetSymbolAddress returned a null address for the static sort scratch");
+        g_static_scratch_addr[dev] = static_cast<unsigned char *>(ptr);
+    }
+    return g_static_scratch_addr[dev];
+}
+
+int sort_trajectories_by_lh_static(kb_trajectory *d_list, uint64_t n, cudaStream_t st) {
+    if (n > kStaticSortMax)
+        throw Error("kb_sort_trajectories_static: " + std::to_string(n) + " trajectories exceed the fixed scratch (" +
+                    std::to_string(kStaticSortMax) + " at most); use the allocating path for longer lists");
+    if (n <= 1) return 0;
+    unsigned char *base = static_scratch_for_current_device();
+    ResultScratch scr;  // a view into the static array; never freed
+    uint32_t *w = reinterpret_cast<uint32_t *>(base);
+    scr.keys[0] = w;
+    scr.keys[1] = w + kStaticSortMax;
+    scr.vals[0] = w + 2 * kStaticSortMax;
+    scr.vals[1] = w + 3 * kStaticSortMax;
+    scr.hist = w + 4 * kStaticSortMax;
+    kb_trajectory *tmp = reinterpret_cast<kb_trajectory *>(w + 4 * kStaticSortMax + kStaticHistWords);
+    // Nothing in the scratch has to start at zero: the key/index buffers are written before they are read, every
+    // histogram word a pass reads is rewritten by that pass's histogram kernel first, and the staging copy is
+    // fully overwritten by the permutation.  (The per-CTA digit counters live in shared memory and are cleared
+    // inside the kernel.)
+    const unsigned gs = (unsigned)((n + 255) / 256);
+    traj_keys_kernel<<<gs, 256, 0, st>>>(d_list, n, scr.keys[0], scr.vals[0]);
+    int launches = 1 + radix_sort_pairs(scr, n, st);
+    traj_permute_kernel<<<gs, 256, 0, st>>>(d_list, scr.vals[0], n, tmp);
+    KB_CUDA(cudaMemcpyAsync(d_list, tmp, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToDevice, st));
+    KB_CUDA(cudaGetLastError());
+    return launches + 1;
+}
+
 }  // namespace kb
+
+extern "C" int kb_sort_trajectories_static(kb_trajectory *d_list, uint64_t n, void *cuda_stream) {
+    KB_API_BEGIN
+    if (!d_list && n) throw kb::Error("kb_sort_trajectories_static: null list");
+    kb::sort_trajectories_by_lh_static(d_list, n, static_cast<cudaStream_t>(cuda_stream));
+    KB_API_END
+}
