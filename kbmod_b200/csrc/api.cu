@@ -79,6 +79,7 @@ struct kb_stack_s {
     DevBuf<kb_trajectory> d_results, d_tmp;
     uint64_t n_results = 0;
     ResultScratch scratch;
+    ClipScratch clip;
     kb_timing timing{};
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
 };
@@ -223,6 +224,7 @@ static void destroy_handle(kb_handle h) {
         if (h->host_pinned) cudaFreeHost(h->host_array); else free(h->host_array);
     }
     result_scratch_free(h->scratch);
+    clip_scratch_free(h->clip);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_stop) cudaEventDestroy(h->ev_stop);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -555,7 +557,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_search.start(st);
     uint32_t sl = 0;
     try {
-        if (plan) sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, st);
+        if (plan) sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st);
         else sl = launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
     } catch (...) {
         if (plan) tiled_plan_destroy(plan);

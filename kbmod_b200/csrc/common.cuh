@@ -83,13 +83,34 @@ int launch_curves(const void *d_ref_layout, const double *d_times, int T, int H,
                   float psi_scale, float phi_min, float phi_scale, const kb_trajectory *d_trjs, uint64_t n,
                   float *d_out, cudaStream_t st);
 
+// Deferred sigma-G clips (search_tiled.cu -> results.cu).  The tiled kernel does not clip in line: a candidate whose
+// unclipped lh reaches min_lh is appended to a global queue; a second kernel clips the queue with every SM (the
+// requests cluster around bright sources, so clipping inside the tile's CTA leaves a few SMs with all the work);
+// the few survivors are then merged into the per-pixel slots.
+struct ClipSurvivor {
+    uint32_t pixel;  // start-pixel index yi * search_width + xi
+    int cand;
+    float lh, flux;
+    int obs;
+};
+struct ClipScratch {
+    uint2 *queue = nullptr;  // {pixel, candidate}
+    ClipSurvivor *surv = nullptr;
+    unsigned long long *counters = nullptr;  // [0] requests (may exceed cap), [1] survivors, [2] clipped in line
+    uint64_t cap = 0;
+};
+void clip_scratch_free(ClipScratch &c);
+struct ResultScratch;
+int merge_clip_survivors(const ClipSurvivor *d_surv, uint64_t n, Slot *d_slots, int K, ResultScratch &scr,
+                         cudaStream_t st);
+
 // search_tiled.cu
 struct TiledPlan;  // opaque: schedule for the TMA-staged kernel
 // Returns nullptr (and a reason) when the tiled kernel cannot be used for this search.
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
                              uint64_t n_cand, cudaStream_t st, std::string *why_not);
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
-                        const float *d_vy, Slot *d_slots, cudaStream_t st);
+                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st);
 void tiled_plan_destroy(TiledPlan *plan);
 
 // psi_phi.cu

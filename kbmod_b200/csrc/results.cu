@@ -364,6 +364,56 @@ int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &sc
     return launches + 1;
 }
 
+// ---- merging deferred sigma-G survivors into the per-pixel slots ------------------------------------------------
+__global__ void surv_keys_kernel(const ClipSurvivor *__restrict__ surv, uint64_t n, uint32_t *keys, uint32_t *vals) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = surv[i].pixel;
+    vals[i] = (uint32_t)i;
+}
+
+// One thread per run of equal pixel keys (sorted): insert the run's survivors into that pixel's K slots, which are
+// kept in descending (lh, then ascending candidate index) order -- the order the tiled kernel uses.
+__global__ void surv_merge_kernel(const ClipSurvivor *__restrict__ surv, const uint32_t *__restrict__ keys,
+                                  const uint32_t *__restrict__ order, uint64_t n, Slot *slots, int K) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t pix = keys[i];
+    if (i > 0 && keys[i - 1] == pix) return;  // not the first of its run
+    Slot *my = slots + (size_t)pix * K;
+    for (uint64_t j = i; j < n && keys[j] == pix; ++j) {
+        const ClipSurvivor sv = surv[order[j]];
+        Slot cur{sv.lh, sv.flux, sv.obs, sv.cand};
+        for (int r = 0; r < K; ++r) {
+            const Slot s = my[r];
+            if (cur.lh > s.lh || (cur.lh == s.lh && cur.cand < s.cand)) {
+                my[r] = cur;
+                cur = s;
+            }
+        }
+    }
+}
+
+int merge_clip_survivors(const ClipSurvivor *d_surv, uint64_t n, Slot *d_slots, int K, ResultScratch &scr,
+                         cudaStream_t st) {
+    if (n == 0) return 0;
+    if (n >= (1ull << 32)) throw Error("Too many sigma-G survivors for 32-bit indices.");
+    ensure_scratch(scr, n, 1);
+    const unsigned gs = (unsigned)((n + 255) / 256);
+    surv_keys_kernel<<<gs, 256, 0, st>>>(d_surv, n, scr.keys[0], scr.vals[0]);
+    int launches = 1 + radix_sort_pairs(scr, n, st);
+    surv_merge_kernel<<<gs, 256, 0, st>>>(d_surv, scr.keys[0], scr.vals[0], n, d_slots, K);
+    KB_CUDA(cudaGetLastError());
+    return launches + 1;
+}
+
+void clip_scratch_free(ClipScratch &c) {
+    if (c.queue) cudaFree(c.queue);
+    if (c.surv) cudaFree(c.surv);
+    if (c.counters) cudaFree(c.counters);
+    c = ClipScratch();
+}
+
 // ---- sorting a trajectory list without allocating anything ----------------------------------------------------
 // The scratch the radix sort needs (two key buffers, two index buffers, the digit histograms and a staging copy of
 // the list) lives in one file-scope device array instead of cudaMalloc'd buffers.  Every GPU that loads this

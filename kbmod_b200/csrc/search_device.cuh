@@ -188,7 +188,7 @@ __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *t
     if (n < min_obs || n == 0) return;
     // rank[e] = position of my element in ascending order (ties: earlier image first)
     int rank[E];
-    bool tie_bad = false;
+    bool has_tie = false;
 #pragma unroll
     for (int e = 0; e < E; ++e) rank[e] = 0;
 #pragma unroll
@@ -198,21 +198,39 @@ __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *t
             const int ls = __ffs(m) - 1;
             m &= m - 1;
             const float v = __shfl_sync(FULL, lc[es], ls);
-            const float va = __shfl_sync(FULL, a[es], ls);
-            const float vb = __shfl_sync(FULL, b[es], ls);
             const int ts = es * 32 + ls;
 #pragma unroll
             for (int e = 0; e < E; ++e) {
                 const int t = e * 32 + lane;
                 const bool eq = (v == lc[e]);
                 if (v < lc[e] || (eq && ts < t)) rank[e] += 1;
-                if (ok[e] && eq && ts != t && (va != a[e] || vb != b[e])) tie_bad = true;
+                has_tie |= ok[e] && eq && ts != t;
             }
         }
     }
-    if (__any_sync(FULL, tie_bad)) {
-        needs_serial = true;
-        return;
+    if (__any_sync(FULL, has_tie)) {
+        // Equal lc values: harmless when the tied observations carry identical (psi, phi); otherwise the
+        // reference's tie order matters for the rounding of the sums and the serial routine must decide.
+        bool tie_bad = false;
+#pragma unroll
+        for (int es = 0; es < E; ++es) {
+            unsigned m = okm[es];
+            while (m) {
+                const int ls = __ffs(m) - 1;
+                m &= m - 1;
+                const float v = __shfl_sync(FULL, lc[es], ls);
+                const float va = __shfl_sync(FULL, a[es], ls);
+                const float vb = __shfl_sync(FULL, b[es], ls);
+                const int ts = es * 32 + ls;
+#pragma unroll
+                for (int e = 0; e < E; ++e)
+                    if (ok[e] && v == lc[e] && ts != e * 32 + lane && (va != a[e] || vb != b[e])) tie_bad = true;
+            }
+        }
+        if (__any_sync(FULL, tie_bad)) {
+            needs_serial = true;
+            return;
+        }
     }
     // kernels.cu:94-127 percentile ranks
     if ((double)sgl_L < 0.0001) sgl_L = (float)0.0001;

@@ -74,6 +74,9 @@ struct PlanView {
     const int *cand;         // [n_groups][TG]  candidate index or -1
     const int *exact;        // candidates evaluated by the exact routine
     int n_exact, n_groups, n_stages, w_base, w_step, max_ch, T;
+    uint2 *clipq;                   // deferred sigma-G requests {start-pixel index, candidate}
+    unsigned long long *clip_cnt;  // [0] requests, [1] survivors, [2] clipped in line (queue full)
+    unsigned long long clip_cap;
 };
 
 struct TiledPlan {
@@ -128,9 +131,11 @@ struct PairLoad;
 template <>
 struct PairLoad<4> {
     static constexpr int kPairBytes = 8;
-    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &, float &psi, float &phi) {
+    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
         asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(psi), "=f"(phi) : "r"(addr));
-        return phi == phi;  // canonical copy: an invalid pair is (NaN, NaN)
+        // canonical copy: an invalid pair is (+0, +0) in zero-marker form, else (NaN, NaN)
+        if (sv.zero_marker) return ((__float_as_uint(psi) | __float_as_uint(phi)) << 1) != 0u;
+        return phi == phi;
     }
 };
 // Encoded stacks: the host verified (plan creation) that fmaf((float)(code-1), scale, min) reproduces the
@@ -165,9 +170,10 @@ struct PairLoad<1> {
 
 // ---- the kernel -----------------------------------------------------------------------------------------
 // ZM (float stacks in zero-marker form, StackView::zero_marker): invalid pairs and out-of-image pixels read as
-// (+0, +0), so the inner loop adds unconditionally and keeps no per-candidate observation count; the count is
-// recovered by re-gathering for the few candidates whose lh reaches the bar.
-template <int NB, bool ZM, bool SIGMAG, int MAXT, int K>
+// (+0, +0), so the inner loop adds unconditionally.
+// COUNT: keep a per-candidate observation count in registers.  Only needed when sigma-G is off and min_obs > 0;
+// with sigma-G on, the count of the few candidates that reach min_lh falls out of the clip's own re-gather.
+template <int NB, bool ZM, bool COUNT, bool SIGMAG, int MAXT, int K>
 __global__ void __launch_bounds__(TNT, 1)
         search_tiled_kernel(const __grid_constant__ TmapSet maps, const PlanView pv, const StackView sv,
                             const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
@@ -236,15 +242,17 @@ __global__ void __launch_bounds__(TNT, 1)
     } else {
         // ===================== consumer warps: gather, reduce, rank ========================================
         const int px = tile_x0 + lane, py = tile_y0 + warp;
+        const bool in_bounds = (px - p.x_start_min) < sw && (py - p.y_start_min) < sh;
+        const unsigned pixel_index = (unsigned)((py - p.y_start_min) * sw + (px - p.x_start_min));
         float psi[TG], phi[TG];
-        int cnt[ZM ? 1 : TG];
+        int cnt[COUNT ? TG : 1];
         TopK<K> top;
         top.init();
 #pragma unroll
         for (int j = 0; j < TG; ++j) {
             psi[j] = 0.0f;
             phi[j] = 0.0f;
-            if (!ZM) cnt[j] = 0;
+            if (COUNT) cnt[j] = 0;
         }
         for (int s = 0; s < n_stages; ++s) {
             const int slot = s % TS;
@@ -271,10 +279,11 @@ __global__ void __launch_bounds__(TNT, 1)
                         if (ZM) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
+                            if (COUNT && ok) cnt[j] += 1;
                         } else if (ok) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
-                            cnt[j] += 1;
+                            if (COUNT) cnt[j] += 1;
                         }
                     }
                 }
@@ -291,12 +300,12 @@ __global__ void __launch_bounds__(TNT, 1)
                     psi[j] = 0.0f;
                     phi[j] = 0.0f;
                     int seen = 0;
-                    if (!ZM) {
+                    if (COUNT) {
                         seen = cnt[j];
                         cnt[j] = 0;
                     }
                     if (c < 0) continue;
-                    bool alive = ZM || seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
+                    bool alive = !COUNT || seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
                     // Conservative reject: est approximates lh to ~1e-6 relative; anything clearly below the
                     // bar (min_lh when sigma-G is on, else the current K-th best) cannot matter.
                     const float bar_lh = SIGMAG ? p.min_lh : top.worst();
@@ -306,24 +315,38 @@ __global__ void __launch_bounds__(TNT, 1)
                         if (!alive) continue;
                         float lh, flux;
                         finish_sums(ps, ph, lh, flux);
-                        if (!beats(lh, c, top.worst(), top.cand[K - 1])) continue;
-                        if (ZM && p.min_observations > 0 &&
-                            count_observations<NB>(sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c)) <
-                                    p.min_observations)
-                            continue;
-                        top.insert(lh, c);
+                        if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
                     } else {
                         if (!__any_sync(0xffffffffu, alive)) continue;
                         float lh = -1.0f, flux = -1.0f;
                         if (alive) finish_sums(ps, ph, lh, flux);
                         alive = alive && !(lh < p.min_lh);  // kernels.cu:201-203 then :319
-                        const bool need = alive && (ZM || seen != 0);
-                        int nv = seen;
-                        sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, __ldg(cvx + c), __ldg(cvy + c), p, lh,
-                                                   flux, nv);
-                        if (ZM && need && nv < p.min_observations) alive = false;
-                        alive = alive && !(lh < p.min_lh);
-                        if (alive && beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
+                        // The clip itself is deferred: append (pixel, candidate) to the global queue; clip_kernel
+                        // works it off afterwards with every SM (the requests cluster around bright sources).
+                        alive = alive && in_bounds;
+                        const unsigned am = __ballot_sync(0xffffffffu, alive);
+                        if (am) {
+                            unsigned long long base_slot = 0;
+                            if (lane == 0) base_slot = atomicAdd(pv.clip_cnt, (unsigned long long)__popc(am));
+                            base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+                            const unsigned long long slot_q = base_slot + __popc(am & ((1u << lane) - 1u));
+                            bool inline_need = false;
+                            if (alive) {
+                                if (slot_q < pv.clip_cap) pv.clipq[slot_q] = make_uint2(pixel_index, (unsigned)c);
+                                else inline_need = true;
+                            }
+                            if (__any_sync(0xffffffffu, inline_need)) {  // queue full: clip it here and now
+                                int nv = 0;
+                                sigmag_for_lanes<NB, MAXT>(inline_need, sv, s_times, px, py, __ldg(cvx + c),
+                                                           __ldg(cvy + c), p, lh, flux, nv);
+                                if (inline_need) {
+                                    atomicAdd(pv.clip_cnt + 2, 1ull);
+                                    if (!(nv < p.min_observations) && !(lh < p.min_lh) &&
+                                        beats(lh, c, top.worst(), top.cand[K - 1]))
+                                        top.insert(lh, c);
+                                }
+                            }
+                        }
                     }
                 }
             }
@@ -601,6 +624,9 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     v.w_step = w_step;
     v.max_ch = max_ch;
     v.T = T;
+    v.clipq = nullptr;
+    v.clip_cnt = nullptr;
+    v.clip_cap = 0;
     plan->smem = (size_t)TS * (STAGE_BYTES + HDR_BYTES) + 2 * TS * 8 + sizeof(double) * (size_t)T;
 
     // ---- tensor maps over the search copy: dims (x elements, rows, images), one per box width ------------------
@@ -633,12 +659,58 @@ void tiled_plan_destroy(TiledPlan *plan) {
     delete plan;
 }
 
-template <int NB, bool ZM, bool SIGMAG, int MAXT>
+// ---- the deferred sigma-G clips: one warp per queued (pixel, candidate), all SMs ------------------------------
+template <int NB, int MAXT>
+__global__ void __launch_bounds__(256)
+        clip_kernel(const StackView sv, const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
+                    const uint2 *__restrict__ queue, unsigned long long *cnt, unsigned long long cap,
+                    ClipSurvivor *__restrict__ surv) {
+    extern __shared__ double s_times[];
+    for (int i = threadIdx.x; i < sv.T; i += blockDim.x) s_times[i] = sv.times[i];
+    __syncthreads();
+    const unsigned long long n = min(cnt[0], cap);
+    const int sw = p.x_start_max - p.x_start_min;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n;
+         i += nwarps) {
+        const uint2 it = queue[i];
+        const int x = p.x_start_min + (int)(it.x % (unsigned)sw), y = p.y_start_min + (int)(it.x / (unsigned)sw);
+        const int c = (int)it.y;
+        float lh = -1.0f, flux = -1.0f;  // what the reference keeps when there is no valid observation at all
+        int nv = 0;
+        sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, __ldg(cvx + c), __ldg(cvy + c), p, lh, flux, nv);
+        if (lane == 0) {
+            // Queued candidates had an unclipped lh >= min_lh.  The clip replaces lh/flux when it ran
+            // (nv >= max(min_obs, 1)); nv < min_obs is rejected (kernels.cu:318); nv == 0 keeps lh = flux = -1.
+            if (!(nv < p.min_observations) && !(lh < p.min_lh)) {
+                const unsigned long long k = atomicAdd(cnt + 1, 1ull);
+                surv[k] = ClipSurvivor{it.x, c, lh, flux, nv};
+            }
+        }
+    }
+}
+
+template <int NB>
+static void launch_clip(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
+                        ClipScratch &clip, cudaStream_t st) {
+    const size_t smem = sizeof(double) * (size_t)sv.T;
+    const int grid = 148 * 8;
+#define KB_CLIP(MT) clip_kernel<NB, MT><<<grid, 256, smem, st>>>(sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv)
+    if (sv.T <= 32) KB_CLIP(32);
+    else if (sv.T <= 64) KB_CLIP(64);
+    else if (sv.T <= 256) KB_CLIP(256);
+    else KB_CLIP(kMaxTSigma);
+#undef KB_CLIP
+    KB_CUDA(cudaGetLastError());
+}
+
+template <int NB, bool ZM, bool COUNT, bool SIGMAG, int MAXT>
 static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                      Slot *d_slots, dim3 grid, cudaStream_t st) {
 #define KB_LAUNCH_T(KK)                                                                                         \
     do {                                                                                                        \
-        auto kfn = search_tiled_kernel<NB, ZM, SIGMAG, MAXT, KK>;                                                   \
+        auto kfn = search_tiled_kernel<NB, ZM, COUNT, SIGMAG, MAXT, KK>;                                                   \
         KB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan->smem));       \
         kfn<<<grid, TNT, plan->smem, st>>>(plan->maps, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
     } while (0)
@@ -653,18 +725,41 @@ static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, c
 template <int NB, bool ZM>
 static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
-    if (!plan->sigmag) launch_k<NB, ZM, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 32) launch_k<NB, ZM, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 64) launch_k<NB, ZM, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 256) launch_k<NB, ZM, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else launch_k<NB, ZM, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    if (!plan->sigmag) {
+        if (p.min_observations > 0) launch_k<NB, ZM, true, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+        else launch_k<NB, ZM, false, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    } else if (sv.T <= 32) launch_k<NB, ZM, false, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 64) launch_k<NB, ZM, false, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 256) launch_k<NB, ZM, false, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else launch_k<NB, ZM, false, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
-                        const float *d_vy, Slot *d_slots, cudaStream_t st) {
+                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st) {
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
     if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
+    if (plan->sigmag) {
+        // Queue for the deferred clips: every (pixel, candidate) pair if that is small, else 32M requests (256 MB);
+        // the kernel clips in line once the queue is full, so the capacity only affects speed.
+        const uint64_t want = std::min<uint64_t>((uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * TG, 1),
+                                                 32ull << 20);
+        if (!clip.counters) KB_CUDA(cudaMalloc(&clip.counters, 4 * sizeof(unsigned long long)));
+        if (clip.cap < want) {
+            if (clip.queue) cudaFree(clip.queue);
+            if (clip.surv) cudaFree(clip.surv);
+            clip.queue = nullptr;
+            clip.surv = nullptr;
+            clip.cap = 0;
+            KB_CUDA(cudaMalloc(&clip.queue, sizeof(uint2) * want));
+            KB_CUDA(cudaMalloc(&clip.surv, sizeof(ClipSurvivor) * want));
+            clip.cap = want;
+        }
+        KB_CUDA(cudaMemsetAsync(clip.counters, 0, 4 * sizeof(unsigned long long), st));
+        plan->v.clipq = clip.queue;
+        plan->v.clip_cnt = clip.counters;
+        plan->v.clip_cap = clip.cap;
+    }
     switch (sv.nb) {
         case 4:
             if (sv.zero_marker) launch_nb<4, true>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
@@ -675,7 +770,23 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         default: throw Error("bad num_bytes");
     }
     KB_CUDA(cudaGetLastError());
-    return 1;
+    int launches = 1;
+    if (plan->sigmag) {
+        switch (sv.nb) {
+            case 4: launch_clip<4>(sv, p, d_vx, d_vy, clip, st); break;
+            case 2: launch_clip<2>(sv, p, d_vx, d_vy, clip, st); break;
+            default: launch_clip<1>(sv, p, d_vx, d_vy, clip, st); break;
+        }
+        ++launches;
+        unsigned long long cnt[4];
+        KB_CUDA(cudaMemcpyAsync(cnt, clip.counters, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+        KB_CUDA(cudaStreamSynchronize(st));
+        if (getenv("KB_DEBUG"))
+            fprintf(stderr, "[kbmod_b200] sigma-G clips: requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
+                    cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
+        launches += merge_clip_survivors(clip.surv, cnt[1], d_slots, (int)p.results_per_pixel, scr, st);
+    }
+    return launches;
 }
 
 }  // namespace kb
