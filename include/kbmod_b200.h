@@ -62,7 +62,7 @@ typedef struct {
     uint32_t search_launches; /* number of search-kernel launches */
     uint32_t total_launches;  /* all kernels launched by the call */
     uint32_t used_tiled;      /* 1 when the TMA-staged tiled kernel ran, 0 for the generic kernel */
-    uint32_t reserved;
+    float ms_main_kernel;     /* the single gather kernel launch alone (search_tiled_kernel / search_generic_kernel) */
 } kb_timing;
 
 typedef struct kb_stack_s *kb_handle;

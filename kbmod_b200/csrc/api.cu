@@ -208,11 +208,16 @@ static kb_handle new_handle() {
     return h.release();
 }
 
-static void free_device_stack(kb_handle h) {
-    if (h->d_search) cudaFree(h->d_search);
-    if (h->d_times) cudaFree(h->d_times);
-    h->d_search = nullptr;
-    h->d_times = nullptr;
+// keep_alloc: search_all on a stack that is not preloaded uploads it for every search and drops it afterwards
+// (the reference's semantics, stack_search.cpp:243,257).  The device allocation itself is kept for the next
+// upload -- cudaMalloc/cudaFree of a multi-GB block every search costs milliseconds and synchronises the device.
+static void free_device_stack(kb_handle h, bool keep_alloc = false) {
+    if (!keep_alloc) {
+        if (h->d_search) cudaFree(h->d_search);
+        if (h->d_times) cudaFree(h->d_times);
+        h->d_search = nullptr;
+        h->d_times = nullptr;
+    }
     h->on_gpu = false;
 }
 
@@ -236,8 +241,8 @@ static void upload_stack(kb_handle h) {
     if (h->on_gpu) return;
     const size_t pb = pair_bytes(h->nb);
     const size_t rows = (size_t)h->T * h->H;
-    KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
-    KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
+    if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
     KB_CUDA(cudaMemcpy2DAsync(h->d_search, (size_t)h->Wp * pb, h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, rows,
                               cudaMemcpyHostToDevice, h->stream));
@@ -571,6 +576,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_post.start(st);
     uint64_t n_keep = 0;
     launches += filter_count(h->d_slots.p, n_slots, p.min_lh, p.min_observations, h->scratch, &n_keep, st);
+    const float main_ms = plan ? tiled_plan_kernel_ms(plan) : -1.0f;
     if (plan) tiled_plan_destroy(plan);  // the stream is idle here (filter_count synchronised)
     h->d_results.ensure(std::max<uint64_t>(n_keep, 1));
     bool invalid = false;
@@ -587,10 +593,11 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     h->timing.ms_h2d = t_h2d.ms();
     h->timing.ms_prepare = t_prep.ms();
     h->timing.ms_search = t_search.ms();
+    h->timing.ms_main_kernel = main_ms >= 0.0f ? main_ms : h->timing.ms_search;
     h->timing.ms_filter_sort = t_post.ms();
     h->timing.ms_total = t_total.ms();
     h->timing.total_launches = launches;
-    if (!was_on_gpu) free_device_stack(h);  // search_all frees the stack again unless preloaded (:257)
+    if (!was_on_gpu) free_device_stack(h, true);  // search_all drops the stack again unless preloaded (:257)
     if (invalid) throw Error("Invalid trajectory detected in the search results.");
     if (n_results) *n_results = n_keep;
     KB_API_END
@@ -694,7 +701,7 @@ int kb_evaluate_trajectories(kb_handle h, const kb_params *params, kb_trajectory
     if (keep_mask)
         KB_CUDA(cudaMemcpyAsync(keep_mask, d_m.p, n * (uint64_t)h->T, cudaMemcpyDeviceToHost, h->stream));
     KB_CUDA(cudaStreamSynchronize(h->stream));
-    if (!was_on_gpu) free_device_stack(h);
+    if (!was_on_gpu) free_device_stack(h, true);
     KB_API_END
 }
 

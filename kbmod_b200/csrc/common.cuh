@@ -112,6 +112,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
                         const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st);
 void tiled_plan_destroy(TiledPlan *plan);
+float tiled_plan_kernel_ms(TiledPlan *plan);  // duration of the gather kernel of the last launch (CUDA events)
 
 // psi_phi.cu
 int launch_convolve(const float *d_img, int H, int W, const float *d_psf, int dim, float psf_total, float *d_out,

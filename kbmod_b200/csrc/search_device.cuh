@@ -159,7 +159,7 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 // when two tied observations carry different (psi, phi).  In that (rare) case *needs_serial is set and the
 // caller falls back to sigmag_recompute for bit-exactness.  Result is warp-uniform.  T <= 32*E.
 template <int NB, int E>
-__device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
+__device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
                                             float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float &lh,
                                             float &flux, int &n_valid, bool &needs_serial) {
     const unsigned FULL = 0xffffffffu;
@@ -286,7 +286,7 @@ __device__ __forceinline__ void warp_sigmag(const StackView &sv, const double *t
 // reference skips the clip, kernels.cu:201-203, and lh/flux are left as they were).
 // MAXT <= 256 selects the cooperative routine (E = MAXT/32); larger stacks use the serial routine.
 template <int NB, int MAXT>
-__device__ __forceinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
+__device__ __noinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
                                                  float vx, float vy, const kb_params &p, float &lh, float &flux,
                                                  int &n_valid) {
     if constexpr (MAXT > 256) {

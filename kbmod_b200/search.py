@@ -740,7 +740,7 @@ class StackSearch:
     def last_timing(self):
         t = KbTiming()
         check(lib.kb_get_timing(self._ppa._require(), C.byref(t)))
-        return {f[0]: getattr(t, f[0]) for f in KbTiming._fields_ if f[0] != "reserved"}
+        return {f[0]: getattr(t, f[0]) for f in KbTiming._fields_}
 
     def get_number_total_results(self):
         n = C.c_uint64(0)
