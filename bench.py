@@ -20,6 +20,7 @@ Only the cpu_baseline leg and --impl reference touch oracle/ (the reference's ow
 """
 import argparse
 import json
+import math
 import os
 import sys
 import threading
@@ -46,30 +47,43 @@ CONFIGS = {
                   min_obs=10, min_lh=10.0, K=8, obs_per_day=4, seed=101, n_obj=20),
     "C3u8": dict(T=20, H=2048, W=2048, psf=1.0, mask=0.01, grid=(50, -40, 40, 40, -32, 32), nb=1, sigmag=True,
                  min_obs=10, min_lh=10.0, K=8, obs_per_day=4, seed=101, n_obj=20),
+    # C4: BASELINE.json configs[3] (psi/phi generation reported as ctor_seconds); C5: configs[4] is an 8-GPU
+    # config -- on one GPU the bench searches ONE of its 8 start-pixel row bands ("band_div": 8) of the full stack.
+    "C4": dict(T=100, H=4096, W=4096, psf=1.0, mask=0.01, ecliptic=([0.5, 8.0, 200], [-math.pi / 15, math.pi / 15, 100]),
+               nb=-1, sigmag=True, min_obs=50, min_lh=10.0, K=8, obs_per_day=4, seed=102, n_obj=20),
+    "C5": dict(T=400, H=2048, W=2048, psf=1.0, mask=0.0, grid=(400, -4.0, 4.0, 250, -2.5, 2.5), nb=-1, sigmag=False,
+               min_obs=200, min_lh=10.0, K=8, obs_per_day=8, intra=0.005, seed=103, n_obj=20, band_div=8),
     "C1": dict(T=10, H=512, W=512, psf=0.5, mask=0.0, kbmodv1=(5, 0, 4, 5, -0.1, 0.1), nb=-1, sigmag=False,
                min_obs=7, min_lh=0.0, K=8, obs_per_day=1, seed=0, n_obj=1),
 }
 
 
 def workload_name(cfg_name, c, n_gpus):
-    gen = "VelocityGridSearch 50x40 (2000 candidates)" if "grid" in c else "KBMODV1Search 5x5 (25 candidates)"
+    if "grid" in c:
+        gen = f"VelocityGridSearch {c['grid'][0]}x{c['grid'][3]} ({c['grid'][0] * c['grid'][3]} candidates)"
+    elif "ecliptic" in c:
+        gen = f"EclipticCenteredSearch {c['ecliptic'][0][2]}x{c['ecliptic'][1][2]} ({c['ecliptic'][0][2] * c['ecliptic'][1][2]} candidates)"
+    else:
+        gen = "KBMODV1Search 5x5 (25 candidates)"
     enc = {-1: "float32", 2: "uint16", 1: "uint8"}[c["nb"]]
     return (f"{cfg_name}: FakeDataSet {c['T']}x{c['H'] * n_gpus}x{c['W']} {enc} psi/phi, {gen}, "
-            f"sigma-G {'on' if c['sigmag'] else 'off'}, min_obs {c['min_obs']}, results_per_pixel {c['K']}")
+            f"sigma-G {'on' if c['sigmag'] else 'off'}, min_obs {c['min_obs']}, results_per_pixel {c['K']}"
+            + (f", one of {c['band_div']} start-pixel row bands per GPU" if c.get("band_div") else ""))
 
 
 def make_inputs(c, n_gpus):
     from kbmod_b200 import fake_data as fd
     from kbmod_b200.search import Trajectory
-    times = fd.create_fake_times(c["T"], 57130.2, obs_per_day=c["obs_per_day"])
+    times = fd.create_fake_times(c["T"], 57130.2, obs_per_day=c["obs_per_day"], intra_night_gap=c.get("intra", 0.01))
     ds = fd.FakeDataSet(c["W"], c["H"] * n_gpus, times, mask_fraction=c["mask"], psf_val=c["psf"], use_seed=c["seed"])
-    if "grid" in c:
-        gen = fd.VelocityGridSearch(*c["grid"])
+    if "grid" in c or "ecliptic" in c:
+        gen = fd.VelocityGridSearch(*c["grid"]) if "grid" in c else fd.EclipticCenteredSearch(*c["ecliptic"])
         ds.insert_random_objects_from_generator(c["n_obj"] * n_gpus, gen, 500.0)
     else:
         gen = fd.KBMODV1Search(*c["kbmodv1"])
         ds.insert_object(Trajectory(x=2, y=0, vx=10.7, vy=15.3, flux=275.0))  # README.md:104
     vx, vy = gen.to_arrays()
+    ds.stack_py.objects = list(ds.trajectories)  # the injected movers (for window-parity checks)
     return ds.stack_py, vx, vy
 
 
@@ -138,8 +152,8 @@ def reference_cpu_setup(c, stack, vx, vy, target_seconds):
     n_cand, T = len(vx), c["T"]
     tmax = float(stack.zeroed_times[-1])
     reach = int(np.ceil(max(np.abs(vx).max(), np.abs(vy).max()) * tmax)) + 1
-    w = int(np.sqrt(max(target_seconds * 3.0e7 * cores / (n_cand * T), 64.0 * 64.0)))
-    w = max(64, min(w, min(c["H"], c["W"]) - 2 * reach if min(c["H"], c["W"]) > 2 * reach + 64 else w))
+    w = int(np.sqrt(max(target_seconds * 3.0e7 * cores / (n_cand * T), 16.0 * 16.0)))
+    w = max(16, min(w, min(c["H"], c["W"]) - 2 * reach if min(c["H"], c["W"]) > 2 * reach + 64 else w))
     side = min(min(c["H"], c["W"]), w + 2 * reach)
     lo = max((side - w) // 2, 0)
     w = min(w, side)
@@ -196,11 +210,16 @@ def run_ours(args, c, cfg_name):
     stack, vx, vy = make_inputs(c, world)
     H_total = c["H"] * world
     band = (rank * c["H"], (rank + 1) * c["H"])
+    rows = c["H"]
+    if c.get("band_div"):  # an N-GPU config measured band by band: this GPU takes a middle band of its frame
+        rows = c["H"] // c["band_div"]
+        mid = rank * c["H"] + c["H"] // 2
+        band = (mid - rows // 2, mid - rows // 2 + rows)
     t0 = time.perf_counter()
     s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"])
     ctor_s = time.perf_counter() - t0
-    configure(s, c, band if world > 1 else None)
-    evals_rank = c["W"] * c["H"] * len(vx) * c["T"]
+    configure(s, c, band if (world > 1 or c.get("band_div")) else None)
+    evals_rank = c["W"] * rows * len(vx) * c["T"]
     evals_job = evals_rank * world
     stack_bytes = s.psi_phi_array.total_array_size
     top_n = 0  # merge everything that survives the filter
@@ -278,7 +297,7 @@ def run_ours(args, c, cfg_name):
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(cfg_name, c, world), "candidates": int(len(vx)),
-                       "start_pixels_per_gpu": c["W"] * c["H"], "evals_per_step": evals_job,
+                       "start_pixels_per_gpu": c["W"] * rows, "evals_per_step": evals_job,
                        "l2": "psi/phi stack (%.0f MB) larger than the 126 MB L2; no flush" % (stack_bytes / 1e6),
                        "parallelism": f"start-pixel row bands x{world}, psi/phi replicated, NCCL all-gather merge"
                        if world > 1 else "single GPU", "results": int(n_results), "ctor_seconds": ctor_s},
