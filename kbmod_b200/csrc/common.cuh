@@ -97,7 +97,8 @@ struct ClipScratch {
     uint2 *queue = nullptr;  // {pixel, candidate}
     ClipSurvivor *surv = nullptr;
     unsigned long long *counters = nullptr;  // [0] requests (may exceed cap), [1] survivors, [2] clipped in line
-    uint64_t cap = 0;
+    uint64_t cap = 0;       // queue capacity (requests)
+    uint64_t surv_cap = 0;  // survivor capacity; the clip kernel is rerun with a larger buffer if it overflows
 };
 void clip_scratch_free(ClipScratch &c);
 struct ResultScratch;

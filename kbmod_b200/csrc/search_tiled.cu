@@ -332,20 +332,26 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
     if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
     if (plan->sigmag) {
-        // Queue for the deferred clips: every (pixel, candidate) pair if that is small, else 32M requests (256 MB);
-        // the kernel clips in line once the queue is full, so the capacity only affects speed.
+        // Queue for the deferred clips: every (pixel, candidate) pair if that is small, else 256M requests (2 GB of
+        // the 180 GB); the kernel clips in line once the queue is full, so the capacity only affects speed (C4 with
+        // 20 bright movers raises 108M requests).  Survivors are a small fraction: their buffer starts at 1/8.
         const uint64_t want = std::min<uint64_t>((uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * TG, 1),
-                                                 32ull << 20);
+                                                 256ull << 20);
         if (!clip.counters) KB_CUDA(cudaMalloc(&clip.counters, 4 * sizeof(unsigned long long)));
         if (clip.cap < want) {
             if (clip.queue) cudaFree(clip.queue);
-            if (clip.surv) cudaFree(clip.surv);
             clip.queue = nullptr;
-            clip.surv = nullptr;
             clip.cap = 0;
             KB_CUDA(cudaMalloc(&clip.queue, sizeof(uint2) * want));
-            KB_CUDA(cudaMalloc(&clip.surv, sizeof(ClipSurvivor) * want));
             clip.cap = want;
+        }
+        const uint64_t want_surv = std::min<uint64_t>(want, std::max<uint64_t>(want / 8, 4ull << 20));
+        if (clip.surv_cap < want_surv) {
+            if (clip.surv) cudaFree(clip.surv);
+            clip.surv = nullptr;
+            clip.surv_cap = 0;
+            KB_CUDA(cudaMalloc(&clip.surv, sizeof(ClipSurvivor) * want_surv));
+            clip.surv_cap = want_surv;
         }
         KB_CUDA(cudaMemsetAsync(clip.counters, 0, 4 * sizeof(unsigned long long), st));
         plan->v.clipq = clip.queue;
@@ -367,15 +373,25 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
     KB_CUDA(cudaEventRecord(plan->ev1, st));
     int launches = 1;
     if (plan->sigmag) {
-        switch (sv.nb) {
-            case 4: launch_clip_nb4(sv, p, d_vx, d_vy, clip, st); break;
-            case 2: launch_clip_nb2(sv, p, d_vx, d_vy, clip, st); break;
-            default: launch_clip_nb1(sv, p, d_vx, d_vy, clip, st); break;
-        }
-        ++launches;
         unsigned long long cnt[4];
-        KB_CUDA(cudaMemcpyAsync(cnt, clip.counters, sizeof(cnt), cudaMemcpyDeviceToHost, st));
-        KB_CUDA(cudaStreamSynchronize(st));
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            switch (sv.nb) {
+                case 4: launch_clip_nb4(sv, p, d_vx, d_vy, clip, st); break;
+                case 2: launch_clip_nb2(sv, p, d_vx, d_vy, clip, st); break;
+                default: launch_clip_nb1(sv, p, d_vx, d_vy, clip, st); break;
+            }
+            ++launches;
+            KB_CUDA(cudaMemcpyAsync(cnt, clip.counters, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+            KB_CUDA(cudaStreamSynchronize(st));
+            if (cnt[1] <= clip.surv_cap) break;
+            // more survivors than the buffer holds: enlarge it and clip the (intact) queue again
+            cudaFree(clip.surv);
+            clip.surv = nullptr;
+            clip.surv_cap = 0;
+            KB_CUDA(cudaMalloc(&clip.surv, sizeof(ClipSurvivor) * cnt[1]));
+            clip.surv_cap = cnt[1];
+            KB_CUDA(cudaMemsetAsync(clip.counters + 1, 0, sizeof(unsigned long long), st));
+        }
         if (getenv("KB_DEBUG"))
             fprintf(stderr, "[kbmod_b200] sigma-G clips: requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
                     cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);

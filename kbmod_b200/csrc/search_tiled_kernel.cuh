@@ -358,7 +358,7 @@ template <int NB, int MAXT>
 __global__ void __launch_bounds__(256)
         clip_kernel(const StackView sv, const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
                     const uint2 *__restrict__ queue, unsigned long long *cnt, unsigned long long cap,
-                    ClipSurvivor *__restrict__ surv) {
+                    ClipSurvivor *__restrict__ surv, unsigned long long surv_cap) {
     extern __shared__ double s_times[];
     for (int i = threadIdx.x; i < sv.T; i += blockDim.x) s_times[i] = sv.times[i];
     __syncthreads();
@@ -378,8 +378,8 @@ __global__ void __launch_bounds__(256)
             // Queued candidates had an unclipped lh >= min_lh.  The clip replaces lh/flux when it ran
             // (nv >= max(min_obs, 1)); nv < min_obs is rejected (kernels.cu:318); nv == 0 keeps lh = flux = -1.
             if (!(nv < p.min_observations) && !(lh < p.min_lh)) {
-                const unsigned long long k = atomicAdd(cnt + 1, 1ull);
-                surv[k] = ClipSurvivor{it.x, c, lh, flux, nv};
+                const unsigned long long k = atomicAdd(cnt + 1, 1ull);  // counts past surv_cap too: host reruns
+                if (k < surv_cap) surv[k] = ClipSurvivor{it.x, c, lh, flux, nv};
             }
         }
     }
@@ -390,7 +390,7 @@ static void launch_clip(const StackView &sv, const kb_params &p, const float *d_
                         ClipScratch &clip, cudaStream_t st) {
     const size_t smem = sizeof(double) * (size_t)sv.T;
     const int grid = 148 * 8;
-#define KB_CLIP(MT) clip_kernel<NB, MT><<<grid, 256, smem, st>>>(sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv)
+#define KB_CLIP(MT) clip_kernel<NB, MT><<<grid, 256, smem, st>>>(sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv, clip.surv_cap)
     if (sv.T <= 32) KB_CLIP(32);
     else if (sv.T <= 64) KB_CLIP(64);
     else if (sv.T <= 256) KB_CLIP(256);
