@@ -21,10 +21,12 @@ __global__ void __launch_bounds__(GX *GY)
 
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     const int xi = blockIdx.x * GX + threadIdx.x, yi = blockIdx.y * GY + threadIdx.y;
-    if (xi >= sw || yi >= sh) return;
+    // Threads past the search bounds stay in the loop (the sigma-G clip is warp-cooperative and needs whole
+    // warps); they just never write.
+    const bool active = xi < sw && yi < sh;
     const int x = xi + p.x_start_min, y = yi + p.y_start_min;
     const int K = (int)p.results_per_pixel;
-    Slot *my = slots + ((size_t)yi * sw + xi) * K;
+    Slot *my = slots + (active ? ((size_t)yi * sw + xi) * K : 0);
     const bool in_regs = K <= kMaxRegK;
 
     // Per-pixel sorted list: registers when K <= 8, else the output slots themselves (kernels.cu:293-301).
@@ -37,7 +39,7 @@ __global__ void __launch_bounds__(GX *GY)
         r_obs[r] = 0;
         r_cand[r] = -1;
     }
-    if (!in_regs)
+    if (!in_regs && active)
         for (int r = 0; r < K; ++r) my[r] = Slot{-FLT_MAX, 0.0f, 0, -1};
 
     for (uint64_t c = 0; c < n_cand; ++c) {
@@ -56,11 +58,11 @@ __global__ void __launch_bounds__(GX *GY)
         float lh, flux;
         finish_sums(psi_sum, phi_sum, lh, flux);
         if (SIGMAG) {
-            if (!(seen < p.min_observations || seen == 0 || lh < p.min_lh))
-                sigmag_recompute<NB, MAXT>(sv, s_times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
-                                           nullptr);
+            const bool need = active && !(seen < p.min_observations || seen == 0 || lh < p.min_lh);
+            int nv = seen;
+            sigmag_for_lanes<NB, MAXT>(need, sv, s_times, x, y, vx, vy, p, lh, flux, nv);  // all lanes take part
         }
-        if (seen < p.min_observations || (SIGMAG && lh < p.min_lh)) continue;  // kernels.cu:318-320
+        if (!active || seen < p.min_observations || (SIGMAG && lh < p.min_lh)) continue;  // kernels.cu:318-320
         int cc = (int)c;
         if (in_regs) {
             if (!(lh > r_lh[kMaxRegK - 1])) continue;
@@ -85,7 +87,7 @@ __global__ void __launch_bounds__(GX *GY)
             }
         }
     }
-    if (in_regs) {
+    if (in_regs && active) {
 #pragma unroll
         for (int r = 0; r < kMaxRegK; ++r)
             if (r < K) my[r] = Slot{r_lh[r], r_flux[r], r_obs[r], r_cand[r]};
@@ -108,6 +110,8 @@ static int launch_generic_nb(const StackView &sv, const kb_params &p, const floa
     } while (0)
     if (!p.do_sigmag_filter) {
         KB_LAUNCH_G(false, 1);
+    } else if (sv.T <= 32) {
+        KB_LAUNCH_G(true, 32);
     } else if (sv.T <= 64) {
         KB_LAUNCH_G(true, 64);
     } else if (sv.T <= 256) {

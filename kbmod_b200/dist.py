@@ -59,7 +59,17 @@ class Comm:
                 uid = torch.tensor(list(buf), dtype=torch.uint8)
             td.broadcast(uid, src=0)
             buf = (C.c_uint8 * 128)(*uid.tolist())
-            check(lib.kb_nccl_init(buf, C.c_int(rank), C.c_int(world)))
+            # NCCL may print its version banner on stdout (NCCL_DEBUG=VERSION); callers such as bench.py promise
+            # exactly one JSON line there, so route fd 1 to stderr while the communicator comes up.
+            import sys
+            sys.stdout.flush()
+            saved = os.dup(1)
+            try:
+                os.dup2(2, 1)
+                check(lib.kb_nccl_init(buf, C.c_int(rank), C.c_int(world)))
+            finally:
+                os.dup2(saved, 1)
+                os.close(saved)
             self.nccl = True
 
     def barrier(self):
