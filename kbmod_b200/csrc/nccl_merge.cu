@@ -33,6 +33,25 @@ struct NcclApi {
 };
 static NcclApi g_nccl;
 
+// Grow-only device buffers of the merge (one communicator per process): cudaMalloc/cudaFree synchronise the
+// device, which showed up in the 8-GPU step time when they ran every merge.
+struct MergeBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    void *ensure(size_t bytes) {
+        if (bytes > cap) {
+            if (p) cudaFree(p);
+            p = nullptr;
+            cap = 0;
+            const size_t want = bytes + bytes / 4 + 4096;
+            KB_CUDA(cudaMalloc(&p, want));
+            cap = want;
+        }
+        return p;
+    }
+};
+static MergeBuf g_counts, g_send, g_all, g_cat;
+
 static void nccl_load() {
     if (g_nccl.lib) return;
     const char *env = getenv("KB_NCCL_LIB");
@@ -93,6 +112,11 @@ int kb_nccl_finalize(void) {
         KB_NCCL(g_nccl.CommDestroy(g_nccl.comm));
         g_nccl.comm = nullptr;
     }
+    for (MergeBuf *b : {&g_counts, &g_send, &g_all, &g_cat}) {
+        if (b->p) cudaFree(b->p);
+        b->p = nullptr;
+        b->cap = 0;
+    }
     KB_API_END
 }
 
@@ -107,14 +131,12 @@ int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results)
     uint64_t n_send = (top_n && top_n < n_local) ? top_n : n_local;
 
     // 1. counts
-    uint64_t *d_counts = nullptr;
-    KB_CUDA(cudaMalloc(&d_counts, sizeof(uint64_t) * (world + 1)));
+    uint64_t *d_counts = static_cast<uint64_t *>(g_counts.ensure(sizeof(uint64_t) * (world + 1)));
     KB_CUDA(cudaMemcpyAsync(d_counts + world, &n_send, sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     KB_NCCL(g_nccl.AllGather(d_counts + world, d_counts, 1, NCCL_UINT64, g_nccl.comm, st));
     std::vector<uint64_t> counts(world);
     KB_CUDA(cudaMemcpyAsync(counts.data(), d_counts, sizeof(uint64_t) * world, cudaMemcpyDeviceToHost, st));
     KB_CUDA(cudaStreamSynchronize(st));
-    cudaFree(d_counts);
     uint64_t max_c = 0, total = 0;
     for (uint64_t c : counts) { max_c = std::max(max_c, c); total += c; }
 
@@ -124,11 +146,10 @@ int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results)
         return 0;
     }
     // 2. padded blocks
-    kb_trajectory *d_send = nullptr, *d_all = nullptr, *d_cat = nullptr;
     const size_t blk = sizeof(kb_trajectory) * max_c;
-    KB_CUDA(cudaMalloc(&d_send, blk));
-    KB_CUDA(cudaMalloc(&d_all, blk * world));
-    KB_CUDA(cudaMalloc(&d_cat, sizeof(kb_trajectory) * total));
+    kb_trajectory *d_send = static_cast<kb_trajectory *>(g_send.ensure(blk));
+    kb_trajectory *d_all = static_cast<kb_trajectory *>(g_all.ensure(blk * world));
+    kb_trajectory *d_cat = static_cast<kb_trajectory *>(g_cat.ensure(sizeof(kb_trajectory) * total));
     KB_CUDA(cudaMemsetAsync(d_send, 0, blk, st));
     if (n_send) KB_CUDA(cudaMemcpyAsync(d_send, d_local, sizeof(kb_trajectory) * n_send, cudaMemcpyDeviceToDevice, st));
     KB_NCCL(g_nccl.AllGather(d_send, d_all, blk, NCCL_INT8, g_nccl.comm, st));
@@ -143,9 +164,6 @@ int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results)
     handle_replace_results(h, d_cat, total, true);
     uint64_t keep = (top_n && top_n < total) ? top_n : total;
     handle_replace_results(h, handle_results(h, &n_local), keep, false);
-    cudaFree(d_send);
-    cudaFree(d_all);
-    cudaFree(d_cat);
     if (n_results) *n_results = keep;
     KB_API_END
 }
