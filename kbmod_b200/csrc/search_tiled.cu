@@ -178,6 +178,29 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             stack_.push_back({sg.lo + left, sg.hi});  // popped second: leaves come out in in-order traversal
             stack_.push_back({sg.lo, sg.lo + left});
         }
+        // Order every leaf as a greedy chain of nearest neighbours in velocity space: consecutive candidates then
+        // share their pixel offset on many images, and the kernel skips the repeated shared-memory load.
+        for (const Seg &l : leaves) {
+            int *c = tabulated.data() + l.lo;
+            const int n = l.hi - l.lo;
+            int first = 0;
+            for (int i = 1; i < n; ++i)
+                if (h_vy[c[i]] < h_vy[c[first]] || (h_vy[c[i]] == h_vy[c[first]] && h_vx[c[i]] < h_vx[c[first]])) first = i;
+            std::swap(c[0], c[first]);
+            for (int i = 1; i < n; ++i) {
+                int best = i;
+                double bd = DBL_MAX;
+                for (int k = i; k < n; ++k) {
+                    const double ddx = (double)h_vx[c[k]] - h_vx[c[i - 1]], ddy = (double)h_vy[c[k]] - h_vy[c[i - 1]];
+                    const double d2 = ddx * ddx + ddy * ddy;
+                    if (d2 < bd || (d2 == bd && c[k] < c[best])) {
+                        bd = d2;
+                        best = k;
+                    }
+                }
+                std::swap(c[i], c[best]);
+            }
+        }
         for (const Seg &l : leaves) group_start.push_back(l.lo);
         group_start.push_back(NTab);
     }

@@ -237,6 +237,13 @@ __global__ void __launch_bounds__(TNT, 1)
                 const int pitch = pv.w_base + pv.w_step * (bx.z >> 16);
                 const uint32_t bk = base + bx.w + (uint32_t)((warp * pitch + lane) * PB);
                 const int4 *ofs = reinterpret_cast<const int4 *>(hdr->offs[k]);
+                // Neighbouring candidates of a group often land on the same pixel of an image (always for t ~ 0,
+                // mostly for dense velocity grids); the host orders a group as a chain of nearest neighbours, and
+                // a candidate whose offset equals its predecessor's reuses the pair already in registers.  The
+                // comparison is warp-uniform (offsets are per (candidate, image), not per pixel).
+                float a = 0.0f, b = 0.0f;
+                bool ok = false;
+                int prev_off = -1;  // offsets are >= 0
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
                     const int4 o = ofs[j4];
@@ -244,8 +251,8 @@ __global__ void __launch_bounds__(TNT, 1)
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int j = j4 * 4 + q;
-                        float a, b;
-                        const bool ok = PairLoad<NB>::load(bk + off[q], sv, a, b);
+                        if (off[q] != prev_off) ok = PairLoad<NB>::load(bk + off[q], sv, a, b);
+                        prev_off = off[q];
                         if (ZM) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
