@@ -101,10 +101,11 @@ struct PairLoad;
 template <>
 struct PairLoad<4> {
     static constexpr int kPairBytes = 8;
+    template <bool ZM>
     __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
         asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(psi), "=f"(phi) : "r"(addr));
         // canonical copy: an invalid pair is (+0, +0) in zero-marker form, else (NaN, NaN)
-        if (sv.zero_marker) return ((__float_as_uint(psi) | __float_as_uint(phi)) << 1) != 0u;
+        if (ZM) return ((__float_as_uint(psi) | __float_as_uint(phi)) << 1) != 0u;
         return phi == phi;
     }
 };
@@ -113,6 +114,7 @@ struct PairLoad<4> {
 template <>
 struct PairLoad<2> {
     static constexpr int kPairBytes = 4;
+    template <bool ZM>
     __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
         uint32_t w;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
@@ -126,6 +128,7 @@ struct PairLoad<2> {
 template <>
 struct PairLoad<1> {
     static constexpr int kPairBytes = 2;
+    template <bool ZM>
     __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
         uint16_t h;
         asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(addr));
@@ -239,20 +242,22 @@ __global__ void __launch_bounds__(TNT, 1)
                 const int4 *ofs = reinterpret_cast<const int4 *>(hdr->offs[k]);
                 // Neighbouring candidates of a group often land on the same pixel of an image (always for t ~ 0,
                 // mostly for dense velocity grids); the host orders a group as a chain of nearest neighbours, and
-                // a candidate whose offset equals its predecessor's reuses the pair already in registers.  The
-                // comparison is warp-uniform (offsets are per (candidate, image), not per pixel).
-                float a = 0.0f, b = 0.0f;
-                bool ok = false;
-                int prev_off = -1;  // offsets are >= 0
+                // inside each run of four a candidate whose offset equals its predecessor's reuses the pair already
+                // in registers.  The comparison is warp-uniform (offsets are per (candidate, image), not per pixel);
+                // the four runs stay independent so their loads overlap.  Only where it compiles to predicated
+                // loads (float pairs, no observation counter); the other variants load every time.
+                constexpr bool DEDUP = (NB == 4) && !COUNT;
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
                     const int4 o = ofs[j4];
                     const int off[4] = {o.x, o.y, o.z, o.w};
+                    float a = 0.0f, b = 0.0f;
+                    bool ok = false;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int j = j4 * 4 + q;
-                        if (off[q] != prev_off) ok = PairLoad<NB>::load(bk + off[q], sv, a, b);
-                        prev_off = off[q];
+                        if (!DEDUP || q == 0 || off[q] != off[q - 1])
+                            ok = PairLoad<NB>::template load<ZM>(bk + off[q], sv, a, b);
                         if (ZM) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
@@ -428,7 +433,8 @@ static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, 
         else launch_k<NB, ZM, false, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
     } else if (sv.T <= 32) launch_k<NB, ZM, false, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
     else if (sv.T <= 64) launch_k<NB, ZM, false, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 256) launch_k<NB, ZM, false, true, 256>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    // (a MAXT = 256 instantiation makes ptxas spill the accumulators of the gather loop; the serial sigma-G routine
+    // of the large variant only runs for the K winners of a pixel and when the clip queue overflows)
     else launch_k<NB, ZM, false, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
