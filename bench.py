@@ -293,6 +293,29 @@ def run_ours(args, c, cfg_name):
                 "note": "algorithmic gather bytes (P*N*T pairs) / kernel time; gathers are served from shared "
                         "memory / L2, so the fraction of the HBM copy peak can exceed 1"}
 
+    # The gathers never go to HBM: the stack is staged once into shared memory by TMA, so the binding resource is the
+    # shared-memory pipe.  Measured on this pool by scripts/peaks_micro.cu (profiles/r01_peaks_micro.jsonl):
+    # L2-resident 256 B row gather and LDS.64 bandwidth -- the "L2 gather roofline" the metric names and the
+    # roofline of the resource the kernel actually runs on.
+    micro = os.path.join(ROOT, "profiles", "r01_peaks_micro.jsonl")
+    if os.path.exists(micro):
+        pk = {}
+        for ln in open(micro):
+            ln = ln.strip()
+            if ln.startswith("{"):
+                d = json.loads(ln)
+                pk[d["what"]] = d["GBps"]
+        if "l2_resident_row_gather_256B" in pk:
+            roofline["l2_gather"] = {"peak": pk["l2_resident_row_gather_256B"], "unit": "GB/s",
+                                     "frac": achieved / pk["l2_resident_row_gather_256B"],
+                                     "peak_source": "scripts/peaks_micro.cu, L2-resident 256 B row gather, measured"}
+        if "smem_lds64" in pk and tiled:
+            roofline["shared_memory"] = {"peak": pk["smem_lds64"], "unit": "GB/s", "frac": achieved / pk["smem_lds64"],
+                                         "peak_source": "scripts/peaks_micro.cu, LDS.64 on all SMs, measured",
+                                         "note": "algorithmic gather bytes / time against the LDS.64 peak; pairs "
+                                                 "shared by neighbouring candidates are read once, so this too "
+                                                 "can exceed the bytes actually moved"}
+
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",

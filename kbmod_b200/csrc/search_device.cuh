@@ -161,7 +161,7 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 template <int NB, int E>
 __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
                                             float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float &lh,
-                                            float &flux, int &n_valid, bool &needs_serial) {
+                                            float &flux, int &n_valid, bool &needs_serial, float2 *ws = nullptr) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     float a[E], b[E], lc[E];
@@ -266,6 +266,22 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     }
     const int first = n_lo, last = med + n_hi;
     float ps = 0.0f, ph = 0.0f;
+    if (ws) {
+        // `ws`: 32*E pairs of shared memory owned by this warp.  Scatter every observation to its sorted position,
+        // then add the kept range in ascending-lc order (every lane runs the same chain on broadcast reads).
+#pragma unroll
+        for (int e = 0; e < E; ++e)
+            if (ok[e]) ws[rank[e]] = make_float2(a[e], b[e]);
+        __syncwarp();
+        for (int r = first; r <= last; ++r) {
+            const float2 v = ws[r];
+            ps = __fadd_rn(ps, v.x);
+            ph = __fadd_rn(ph, v.y);
+        }
+        __syncwarp();  // the next call overwrites ws
+        finish_sums(ps, ph, lh, flux);
+        return;
+    }
     for (int r = first; r <= last; ++r) {
 #pragma unroll
         for (int e = 0; e < E; ++e) {
@@ -288,7 +304,7 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
 template <int NB, int MAXT>
 __device__ __noinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
                                                  float vx, float vy, const kb_params &p, float &lh, float &flux,
-                                                 int &n_valid) {
+                                                 int &n_valid, float2 *ws = nullptr) {
     if constexpr (MAXT > 256) {
         if (need) {
             float l2 = lh, f2 = flux;
@@ -313,7 +329,7 @@ __device__ __noinline__ void sigmag_for_lanes(bool need, const StackView &sv, co
         int rn = 0;
         bool serial;
         warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, p.min_observations, rl, rf,
-                           rn, serial);
+                           rn, serial, ws);
         if (lane == L) {
             n_valid = rn;
             if (serial)

@@ -374,6 +374,9 @@ __global__ void __launch_bounds__(256)
     extern __shared__ double s_times[];
     for (int i = threadIdx.x; i < sv.T; i += blockDim.x) s_times[i] = sv.times[i];
     __syncthreads();
+    // per-warp scratch for the ordered sum of the cooperative clip (MAXT pairs each), after the time table
+    float2 *ws = (MAXT <= 256) ? reinterpret_cast<float2 *>(s_times + ((sv.T + 1) & ~1)) + (threadIdx.x >> 5) * MAXT
+                               : nullptr;
     const unsigned long long n = min(cnt[0], cap);
     const int sw = p.x_start_max - p.x_start_min;
     const int lane = threadIdx.x & 31;
@@ -385,7 +388,7 @@ __global__ void __launch_bounds__(256)
         const int c = (int)it.y;
         float lh = -1.0f, flux = -1.0f;  // what the reference keeps when there is no valid observation at all
         int nv = 0;
-        sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, __ldg(cvx + c), __ldg(cvy + c), p, lh, flux, nv);
+        sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, __ldg(cvx + c), __ldg(cvy + c), p, lh, flux, nv, ws);
         if (lane == 0) {
             // Queued candidates had an unclipped lh >= min_lh.  The clip replaces lh/flux when it ran
             // (nv >= max(min_obs, 1)); nv < min_obs is rejected (kernels.cu:318); nv == 0 keeps lh = flux = -1.
@@ -400,11 +403,14 @@ __global__ void __launch_bounds__(256)
 template <int NB>
 static void launch_clip(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                         ClipScratch &clip, cudaStream_t st) {
-    const size_t smem = sizeof(double) * (size_t)sv.T;
+    const size_t tbytes = sizeof(double) * (size_t)((sv.T + 1) & ~1);
     const int grid = 148 * 8;
-#define KB_CLIP(MT) clip_kernel<NB, MT><<<grid, 256, smem, st>>>(sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv, clip.surv_cap)
+#define KB_CLIP(MT)                                                                                              \
+    clip_kernel<NB, MT><<<grid, 256, tbytes + ((MT) <= 256 ? sizeof(float2) * 8 * (MT) : 0), st>>>(              \
+            sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv, clip.surv_cap)
     if (sv.T <= 32) KB_CLIP(32);
     else if (sv.T <= 64) KB_CLIP(64);
+    else if (sv.T <= 128) KB_CLIP(128);
     else if (sv.T <= 256) KB_CLIP(256);
     else KB_CLIP(kMaxTSigma);
 #undef KB_CLIP
