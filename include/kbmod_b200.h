@@ -143,6 +143,28 @@ KB_EXPORT int kb_psi_phi_curves(kb_handle h, const kb_trajectory *trjs, uint64_t
 KB_EXPORT int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl1, float coeff, float width,
                                int *idx_out, int *n_kept);
 
+/* ---- the filter that follows the search in the reference pipeline ----------------------- */
+/* SigmaGClipping.compute_clipped_sigma_g_matrix (filters/sigma_g_filter.py:114-168): lh is n_rows x n_times
+ * float32 (NaN = no data); valid_out (n_rows x n_times bytes) receives 1 where the point lies strictly inside
+ * median -/+ n_sigma_coeff * max(q_high percentile - q_low percentile, 1e-5), percentiles as torch.nanquantile
+ * computes them (linear interpolation, float32).  q_low/q_high are fractions in (0,1); n_sigma_coeff is the
+ * product n_sigma * coeff narrowed to float32; clip_negative != 0 ignores values <= 0 in the percentiles only.
+ * Host pointers; n_times <= 4096. */
+KB_EXPORT int kb_sigmag_clip_matrix(const float *lh, uint64_t n_rows, uint32_t n_times, float q_low, float q_high,
+                                    float n_sigma_coeff, int clip_negative, uint8_t *valid_out);
+/* Results._update_likelihood (results.py:608-645): per row, float32 sums of psi*obs_valid and phi*obs_valid in
+ * numpy's pairwise order; likelihood = psi_sum/sqrt(phi_sum), flux = psi_sum/phi_sum (0 where phi_sum == 0),
+ * obs_count = number of valid points (n_times when obs_valid is NULL). */
+KB_EXPORT int kb_update_likelihood(const float *psi, const float *phi, const uint8_t *obs_valid, uint64_t n_rows,
+                                   uint32_t n_times, double *lh_out, double *flux_out, int64_t *obs_count_out);
+/* apply_clipped_sigma_g (filters/sigma_g_filter.py:171-190) in one call: likelihood curves from psi/phi and the
+ * current obs_valid (results.py:568-606), the clip above, then the likelihood update with the new mask.
+ * obs_valid_io is read when has_obs_valid != 0 and always receives the new mask. */
+KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64_t n_rows, uint32_t n_times,
+                                      float q_low, float q_high, float n_sigma_coeff, int clip_negative,
+                                      uint8_t *obs_valid_io, int has_obs_valid, double *lh_out, double *flux_out,
+                                      int64_t *obs_count_out);
+
 /* ---- measurement hooks (no reference counterpart) ---------------------------------------------------- */
 /* CUDA events recorded on the handle's own stream, so a caller can time a region of calls on the device:
  * kb_timer_start records the start event; kb_timer_stop records the stop event, waits for it and returns the

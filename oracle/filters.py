@@ -1,0 +1,149 @@
+"""TEST INFRASTRUCTURE -- CPU restatement (numpy, float32) of the step that follows the search in the reference
+pipeline: sigma-G clipping of the per-result likelihood curves and the likelihood update.
+
+Follows /root/reference/src/kbmod (kbmod @ 617cd33):
+  * ``lh_curves``                        results.py:568-606   (Results.compute_likelihood_curves)
+  * ``clipped_sigma_g_matrix``           filters/sigma_g_filter.py:114-168 (SigmaGClipping.compute_clipped_sigma_g_matrix),
+                                         whose percentiles are ``torch.nanquantile`` (pytorch 2.x, linear interpolation:
+                                         rank = q*(n_valid-1) in float32, lerp(below, above, rank - floor(rank)))
+  * ``update_likelihood``                results.py:608-645   (Results._update_likelihood; numpy's float32 pairwise sum)
+  * ``find_sigma_g_coeff``               filters/sigma_g_filter.py:47-85
+
+Pinned by tests/test_oracle_pins.py against fixtures produced by the reference's own class
+(tests/golden/make_golden_filters.py -> tests/golden/sigmag_filter_case.npz) and, where /root/reference exists,
+live against it.  Only tests/ may import this module.
+"""
+import math
+
+import numpy as np
+
+f32 = np.float32
+
+
+def find_sigma_g_coeff(low_bnd, high_bnd):
+    """sigma_g_filter.py:47-85 -- 1 / (Phi^-1(high) - Phi^-1(low)), percentiles on a [0, 100] scale."""
+    from scipy.special import erfinv
+    if (high_bnd <= low_bnd) or (low_bnd < 0) or (high_bnd > 100):
+        raise ValueError(f"Invalid percentiles for sigma G coefficient [{low_bnd}, {high_bnd}]")
+
+    def inv(z):
+        sign = -1 if z < 0.5 else 1
+        return float(sign * np.sqrt(2) * erfinv(sign * (2 * z - 1)))
+    return 1 / (inv(high_bnd / 100.0) - inv(low_bnd / 100.0))
+
+
+def lh_curves(psi, phi, obs_valid=None, mask_value=np.nan):
+    """results.py:596-606."""
+    psi = np.asarray(psi, dtype=f32)
+    phi = np.asarray(phi, dtype=f32)
+    valid = (phi != 0) & np.isfinite(psi) & np.isfinite(phi)
+    if obs_valid is not None:
+        valid = valid & np.asarray(obs_valid, dtype=bool)
+    out = np.full(psi.shape, mask_value, dtype=f32)
+    out[valid] = psi[valid] / np.sqrt(phi[valid])
+    return out
+
+
+def _lerp(a, b, w):
+    """torch lerp as its vectorised CPU kernel and its CUDA kernel evaluate it (one fused multiply-add):
+    w < 0.5 -> fma(w, b - a, a), else fma(w - 1, b - a, b).  Emulated in float64: the product of two float32
+    numbers is exact in float64 and the sum is rounded once (double rounding cannot occur for these magnitudes
+    except in sub-ulp corner cases the fixtures would expose)."""
+    a, b, w = f32(a), f32(b), f32(w)
+    d = f32(b - a)
+    if abs(w) < 0.5:
+        return f32(np.float64(w) * np.float64(d) + np.float64(a))
+    return f32(np.float64(f32(w - f32(1))) * np.float64(d) + np.float64(b))
+
+
+def nanquantile_row(row, qs):
+    """torch.nanquantile(row, qs) for one float32 row: sort with NaN last, rank = float32(q * (n - 1))."""
+    v = np.sort(row[~np.isnan(row)])
+    n = v.size
+    out = []
+    for q in qs:
+        if n == 0:
+            out.append(f32(np.nan))
+            continue
+        rank = f32(f32(q) * f32(n - 1))
+        if rank < 0:
+            rank = f32(0)
+        below = int(math.floor(rank))
+        above = int(math.ceil(rank))
+        w = f32(rank - f32(below))
+        out.append(_lerp(v[below], v[above], w))
+    return out
+
+
+def clipped_sigma_g_matrix(lh, low_bnd=25, high_bnd=75, n_sigma=2, clip_negative=False, coeff=None):
+    """sigma_g_filter.py:114-168.  Returns the boolean keep matrix."""
+    lh = np.asarray(lh, dtype=f32)
+    if coeff is None:
+        coeff = find_sigma_g_coeff(low_bnd, high_bnd)
+    qs = [f32(low_bnd / 100.0), f32(0.5), f32(high_bnd / 100.0)]
+    mult = f32(n_sigma * coeff)          # python double product, narrowed when it meets the float32 tensor
+    out = np.zeros(lh.shape, dtype=bool)
+    with np.errstate(invalid="ignore"):
+        for r in range(lh.shape[0]):
+            row = lh[r]
+            masked = np.where(row > 0, row, f32(np.nan)).astype(f32) if clip_negative else row
+            lo, med, hi = nanquantile_row(masked, qs)
+            delta = f32(hi - lo)
+            if delta < f32(1e-5):
+                delta = f32(1e-5)
+            ns = f32(mult * delta)
+            lower, upper = f32(med - ns), f32(med + ns)
+            out[r] = np.isfinite(row) & (row < upper) & (row > lower)
+    return out
+
+
+def update_likelihood(psi, phi, obs_valid=None):
+    """results.py:630-645: (likelihood, flux, obs_count) per row; float32 sums exactly as numpy adds them."""
+    psi = np.asarray(psi, dtype=f32)
+    phi = np.asarray(phi, dtype=f32)
+    R, T = psi.shape
+    if obs_valid is not None:
+        ov = np.asarray(obs_valid, dtype=bool)
+        phi_sum = (phi * ov).sum(axis=1)
+        psi_sum = (psi * ov).sum(axis=1)
+        num_obs = ov.sum(axis=1)
+    else:
+        phi_sum = phi.sum(axis=1)
+        psi_sum = psi.sum(axis=1)
+        num_obs = np.full(R, T)
+    nz = phi_sum != 0
+    lh = np.zeros(R)
+    flux = np.zeros(R)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        lh[nz] = psi_sum[nz] / np.sqrt(phi_sum[nz])
+        flux[nz] = psi_sum[nz] / phi_sum[nz]
+    return lh, flux, num_obs.astype(np.int64)
+
+
+def pairwise_sum_f32(a):
+    """numpy's float32 pairwise summation of a contiguous 1-D array (numpy/_core/src/umath/loops_utils.h.src,
+    ``@TYPE@_pairwise_sum``), restated so the CUDA kernel's order can be checked without numpy internals."""
+    a = np.asarray(a, dtype=f32)
+    n = a.size
+    if n < 8:
+        res = f32(0.0) if n == 0 else None
+        # numpy starts from -0.0 so that the sign of a lone -0.0 survives
+        res = f32(-0.0)
+        for x in a:
+            res = f32(res + x)
+        return res
+    if n <= 128:
+        r = [f32(a[i]) for i in range(8)]
+        i = 8
+        while i < n - (n % 8):
+            for k in range(8):
+                r[k] = f32(r[k] + a[i + k])
+            i += 8
+        res = f32(f32(f32(r[0] + r[1]) + f32(r[2] + r[3])) + f32(f32(r[4] + r[5]) + f32(r[6] + r[7])))
+        while i < n:
+            res = f32(res + a[i])
+            i += 1
+        return res
+    n2 = n // 2
+    n2 -= n2 % 8
+    return f32(pairwise_sum_f32(a[:n2]) + pairwise_sum_f32(a[n2:]))
