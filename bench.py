@@ -207,11 +207,17 @@ def run_ours(args, c, cfg_name):
     dist.set_device(local_rank)
     comm = dist.Comm(rank, world) if world > 1 else None
 
-    stack, vx, vy = make_inputs(c, world)
-    H_total = c["H"] * world
-    band = (rank * c["H"], (rank + 1) * c["H"])
-    rows = c["H"]
-    if c.get("band_div"):  # an N-GPU config measured band by band: this GPU takes a middle band of its frame
+    strong = args.scaling == "strong" and world > 1
+    frames = 1 if strong else world            # strong: the named frame itself, start-pixel rows split over the ranks
+    stack, vx, vy = make_inputs(c, frames)
+    if strong:
+        edges = [round(i * c["H"] / world) for i in range(world + 1)]
+        band = (edges[rank], edges[rank + 1])
+        rows = c["H"] / world                  # per-rank average (the job total is what is reported)
+    else:
+        band = (rank * c["H"], (rank + 1) * c["H"])
+        rows = c["H"]
+    if c.get("band_div") and not strong:  # an N-GPU config measured band by band: this GPU takes a middle band of its frame
         rows = c["H"] // c["band_div"]
         mid = rank * c["H"] + c["H"] // 2
         band = (mid - rows // 2, mid - rows // 2 + rows)
@@ -219,8 +225,8 @@ def run_ours(args, c, cfg_name):
     s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"])
     ctor_s = time.perf_counter() - t0
     configure(s, c, band if (world > 1 or c.get("band_div")) else None)
-    evals_rank = c["W"] * rows * len(vx) * c["T"]
-    evals_job = evals_rank * world
+    evals_rank = c["W"] * (band[1] - band[0] if strong else rows) * len(vx) * c["T"]
+    evals_job = c["W"] * c["H"] * len(vx) * c["T"] if strong else evals_rank * world
     stack_bytes = s.psi_phi_array.total_array_size
     top_n = 0  # merge everything that survives the filter
 
@@ -317,10 +323,11 @@ def run_ours(args, c, cfg_name):
                                                  "can exceed the bytes actually moved"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong" if strong else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(cfg_name, c, world), "candidates": int(len(vx)),
-                       "start_pixels_per_gpu": c["W"] * rows, "evals_per_step": evals_job,
+            "config": {"workload": workload_name(cfg_name, c, frames), "candidates": int(len(vx)),
+                       "start_pixels_per_gpu": int(c["W"] * rows), "evals_per_step": evals_job,
                        "l2": "psi/phi stack (%.0f MB) larger than the 126 MB L2; no flush" % (stack_bytes / 1e6),
                        "parallelism": f"start-pixel row bands x{world}, psi/phi replicated, NCCL all-gather merge"
                        if world > 1 else "single GPU", "results": int(n_results), "ctor_seconds": ctor_s},
@@ -370,6 +377,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = every GPU searches its own copy-sized band of an N-times taller frame (default, "
+                         "the driver's scaling run); strong = the named frame, start-pixel rows split over the GPUs "
+                         "(BASELINE configs C4 / C5)")
     args = ap.parse_args()
     c = CONFIGS[args.config]
     if args.impl == "reference":

@@ -165,6 +165,18 @@ KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64
                                       uint8_t *obs_valid_io, int has_obs_valid, double *lh_out, double *flux_out,
                                       int64_t *obs_count_out);
 
+/* ---- coadded stamps of the results ----------------------------------------------------- */
+/* append_coadds (filters/stamp_filters.py:72-160, nightly = False) over coadd_sum / coadd_mean / coadd_median /
+ * coadd_weighted (core/stamp_utils.py:241-349): for each of the n trajectories (x0, y0, vx, vy as the float64
+ * columns of the reference's result table) the (2*radius+1)^2 stamp centred on int(v*t + p0 + 0.5) is cut from
+ * every image selected by obs_valid (n x T bytes, NULL = all), NaN where there is no image, and coadded over time in
+ * float64 exactly as the reference does; each output is n x S x S float32 (NULL = not wanted).  var may be NULL
+ * unless out_weighted is given.  Host pointers; sci/var are T pointers to H x W float32 images. */
+KB_EXPORT int kb_coadd_stamps(const float *const *sci, const float *const *var, int T, int H, int W,
+                              const double *times, const double *x0, const double *y0, const double *vx,
+                              const double *vy, uint64_t n, int radius, const uint8_t *obs_valid, float *out_sum,
+                              float *out_mean, float *out_median, float *out_weighted);
+
 /* ---- measurement hooks (no reference counterpart) ---------------------------------------------------- */
 /* CUDA events recorded on the handle's own stream, so a caller can time a region of calls on the device:
  * kb_timer_start records the start event; kb_timer_stop records the stop event, waits for it and returns the

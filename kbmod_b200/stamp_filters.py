@@ -1,0 +1,75 @@
+"""Coadded stamps of the search results on the device -- the reference's ``kbmod.filters.stamp_filters.append_coadds``
+(filters/stamp_filters.py:72-160) over ``kbmod.core.stamp_utils`` (extract_stamp_stack, coadd_sum / coadd_mean /
+coadd_median / coadd_weighted, core/stamp_utils.py:16-349), through ``kb_coadd_stamps`` (csrc/stamps.cu).
+
+No CPU path.  Results are float32 ``R x S x S`` arrays (S = 2 * radius + 1), bit-identical to the reference's.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import check, f32, lib, ptr, ptr_array, require_gpu
+
+COADD_TYPES = ("sum", "mean", "median", "weighted")
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def coadd_stamps(sci, var, zeroed_times, x, y, vx, vy, radius, coadd_types=COADD_TYPES, obs_valid=None):
+    """Coadds for R trajectories.  ``sci`` / ``var``: T images (list or T x H x W array); ``x, y, vx, vy``: length-R
+    arrays (the float64 columns of the reference's result table); ``obs_valid``: optional R x T booleans selecting the
+    images of each trajectory (``valid_only``).  Returns {type: float32[R, S, S]}."""
+    require_gpu()
+    if radius <= 0:
+        raise ValueError(f"Invalid stamp radius {radius}")
+    for t in coadd_types:
+        if t not in COADD_TYPES:
+            raise ValueError(f"Unknown coadd type {t}")
+    sci = [f32(a) for a in sci]
+    T = len(sci)
+    if T == 0:
+        raise ValueError("empty image stack")
+    H, W = sci[0].shape
+    need_var = "weighted" in coadd_types
+    if need_var:
+        var = [f32(a) for a in var]
+        if len(var) != T:
+            raise ValueError("science and variance stacks differ in length")
+    times = _f64(zeroed_times)
+    if times.shape != (T,):
+        raise ValueError("one time per image is required")
+    x, y, vx, vy = _f64(x), _f64(y), _f64(vx), _f64(vy)
+    R = x.size
+    if not (y.size == R and vx.size == R and vy.size == R):
+        raise ValueError("x, y, vx, vy must have the same length")
+    ov = None
+    if obs_valid is not None:
+        ov = np.ascontiguousarray(obs_valid, dtype=np.uint8)
+        if ov.shape != (R, T):
+            raise ValueError("Wrong shape for obs_valid")
+    S = 2 * radius + 1
+    out = {t: np.zeros((R, S, S), dtype=np.float32) for t in coadd_types}
+    if R:
+        check(lib.kb_coadd_stamps(ptr_array(sci), ptr_array(var) if need_var else None, C.c_int(T), C.c_int(H), C.c_int(W),
+                                  ptr(times), ptr(x), ptr(y), ptr(vx), ptr(vy), C.c_uint64(R), C.c_int(radius),
+                                  ptr(ov) if ov is not None else None,
+                                  *[ptr(out[t]) if t in out else None for t in COADD_TYPES]))
+    return out
+
+
+def append_coadds(result_data, im_stack, coadd_types, radius, valid_only=True, nightly=False):
+    """filters/stamp_filters.py:72-160 for a reference ``Results``-like table (columns x, y, vx, vy[, obs_valid]; new
+    columns are written through ``result_data.table[name] = array``) and an ``ImageStackPy``-like stack (``sci``,
+    ``var``, ``zeroed_times``)."""
+    if radius <= 0:
+        raise ValueError(f"Invalid stamp radius {radius}")
+    if nightly:
+        raise RuntimeError("kbmod_b200: per-night coadds are not built (nightly=False only)")
+    valid_only = valid_only and "obs_valid" in result_data.colnames
+    ov = np.asarray(result_data["obs_valid"]) if valid_only else None
+    co = coadd_stamps(im_stack.sci, im_stack.var, im_stack.zeroed_times, result_data["x"], result_data["y"],
+                      result_data["vx"], result_data["vy"], radius, tuple(coadd_types), ov)
+    for t, a in co.items():
+        result_data.table[f"coadd_{t}"] = a

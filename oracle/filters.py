@@ -147,3 +147,90 @@ def pairwise_sum_f32(a):
     n2 = n // 2
     n2 -= n2 % 8
     return f32(pairwise_sum_f32(a[:n2]) + pairwise_sum_f32(a[n2:]))
+
+
+# ---- coadded stamps ------------------------------------------------------------------------
+# core/stamp_utils.py:352-398 (extract_stamp), :403-439 (stack), :241-349 (coadds); positions as
+# filters/stamp_filters.py:110-112 -> trajectory_utils.py:64-73 (float64, +0.5, astype(int) = truncation).
+def stamp_positions(times, x0, v):
+    pos = np.asarray(v, dtype=np.float64)[:, None] * np.asarray(times, dtype=np.float64)[None, :] \
+        + np.asarray(x0, dtype=np.float64)[:, None]
+    return (pos + 0.5).astype(int)
+
+
+def extract_stamp_stack(imgs, xs, ys, radius, to_include=None):
+    """T' x S x S float64 stack, NaN where there is no image (np.full(..., np.nan) is float64 in the reference)."""
+    S = 2 * radius + 1
+    sel = range(len(imgs)) if to_include is None else [t for t in range(len(imgs)) if to_include[t]]
+    out = np.full((len(sel), S, S), np.nan)
+    for k, t in enumerate(sel):
+        img = imgs[t]
+        H, W = img.shape
+        for dy in range(S):
+            y = int(ys[t]) - radius + dy
+            if y < 0 or y >= H:
+                continue
+            for dx in range(S):
+                x = int(xs[t]) - radius + dx
+                if 0 <= x < W:
+                    out[k, dy, dx] = img[y, x]
+    return out
+
+
+def coadd_sum(stack):
+    out = np.zeros(stack.shape[1:])
+    for k in range(stack.shape[0]):                      # np.nansum(axis=0): NaN -> 0, added image by image
+        out = out + np.where(np.isnan(stack[k]), 0.0, stack[k])
+    return out
+
+
+def coadd_mean(stack):
+    if stack.shape[0] == 0:
+        return np.zeros(stack.shape[1:])
+    cnt = (~np.isnan(stack)).sum(axis=0)
+    s = coadd_sum(stack)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return np.where(cnt > 0, s / cnt, 0.0)           # all-NaN pixels are zeroed first (stamp_utils.py:214-238)
+
+
+def coadd_median(stack):
+    """torch.nanmedian(dim=0): the LOWER of the two middle values for an even count; all-NaN -> 0."""
+    out = np.zeros(stack.shape[1:])
+    for i in range(stack.shape[1]):
+        for j in range(stack.shape[2]):
+            v = np.sort(stack[:, i, j][~np.isnan(stack[:, i, j])])
+            out[i, j] = v[(v.size - 1) // 2] if v.size else 0.0
+    return out
+
+
+def coadd_weighted(stack, var_stack):
+    if stack.shape[0] == 0:
+        return np.zeros(stack.shape[1:])
+    allnan = np.all(np.isnan(stack), axis=0)
+    stack = np.where(allnan[None], 0.0, stack)
+    ok = ~(np.isnan(stack) | np.isnan(var_stack) | (var_stack == 0.0))
+    wsum = np.zeros(stack.shape[1:])
+    ssum = np.zeros(stack.shape[1:])
+    with np.errstate(invalid="ignore", divide="ignore"):
+        for k in range(stack.shape[0]):
+            w = np.where(ok[k], 1.0 / np.where(ok[k], var_stack[k], 1.0), 0.0)
+            ssum = ssum + np.where(ok[k], stack[k] * w, 0.0)
+            wsum = wsum + w
+    wsum[wsum == 0.0] = 1e24
+    return ssum / wsum
+
+
+def coadds_for_results(sci, var, times, x, y, vx, vy, radius, obs_valid=None):
+    """append_coadds (filters/stamp_filters.py:72-160, nightly=False): float32 R x S x S arrays per coadd type."""
+    xs, ys = stamp_positions(times, x, vx), stamp_positions(times, y, vy)
+    R, S = len(x), 2 * radius + 1
+    out = {k: np.zeros((R, S, S), dtype=np.float32) for k in ("sum", "mean", "median", "weighted")}
+    for r in range(R):
+        inc = None if obs_valid is None else obs_valid[r]
+        st = extract_stamp_stack(sci, xs[r], ys[r], radius, inc)
+        vs = extract_stamp_stack(var, xs[r], ys[r], radius, inc)
+        out["sum"][r] = coadd_sum(st)
+        out["mean"][r] = coadd_mean(st)
+        out["median"][r] = coadd_median(st)
+        out["weighted"][r] = coadd_weighted(st, vs)
+    return out
