@@ -165,6 +165,15 @@ KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64
                                       uint8_t *obs_valid_io, int has_obs_valid, double *lh_out, double *flux_out,
                                       int64_t *obs_count_out);
 
+/* TrajectoryClusterGrid / apply_trajectory_grid_filter (filters/clustering_grid.py:13-176): every trajectory falls
+ * into the spatial bin (int(x/w), int(y/w), int((x + max_time*vx)/w), int((y + max_time*vy)/w)); idx_out receives,
+ * for every occupied bin in the order the bins are first seen, the index of its best trajectory (largest lh; the
+ * earlier one wins a tie); *n_out = number of bins.  f32_product != 0 evaluates max_time*v in float32 as the
+ * vectorised add_trajectory_list does (:109-113), 0 in double as add_trajectory does (:72-75).  Host pointers;
+ * idx_out has room for n entries. */
+KB_EXPORT int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time, int f32_product,
+                             uint32_t *idx_out, uint64_t *n_out);
+
 /* ---- coadded stamps of the results ----------------------------------------------------- */
 /* append_coadds (filters/stamp_filters.py:72-160, nightly = False) over coadd_sum / coadd_mean / coadd_median /
  * coadd_weighted (core/stamp_utils.py:241-349): for each of the n trajectories (x0, y0, vx, vy as the float64

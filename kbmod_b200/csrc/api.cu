@@ -776,6 +776,37 @@ int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl
     KB_API_END
 }
 
+int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time, int f32_product,
+                   uint32_t *idx_out, uint64_t *n_out) {
+    KB_API_BEGIN
+    if (!n_out) throw Error("null argument");
+    *n_out = 0;
+    if (!(bin_width >= 1.0) || !std::isfinite(bin_width))
+        throw Error("Bin width must be at least 1. Got " + std::to_string(bin_width) + ".");
+    if (!(max_time >= 0.0) || !std::isfinite(max_time))
+        throw Error("Max time must be >= 0. Got " + std::to_string(max_time) + ".");
+    if (n == 0) return 0;
+    if (!trjs || !idx_out) throw Error("null argument");
+    int dev_count = 0;
+    if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0)
+        throw Error("no CUDA device: kbmod_b200 has no CPU path");
+    DevBuf<kb_trajectory> d_list;
+    DevBuf<uint32_t> d_idx;
+    d_list.ensure(n);
+    d_idx.ensure(n);
+    KB_CUDA(cudaMemcpy(d_list.p, trjs, sizeof(kb_trajectory) * n, cudaMemcpyHostToDevice));
+    ResultScratch scr;
+    try {
+        grid_filter_indices(d_list.p, n, bin_width, max_time, f32_product, d_idx.p, n_out, scr, 0);
+        KB_CUDA(cudaMemcpy(idx_out, d_idx.p, sizeof(uint32_t) * (*n_out), cudaMemcpyDeviceToHost));
+    } catch (...) {
+        result_scratch_free(scr);
+        throw;
+    }
+    result_scratch_free(scr);
+    KB_API_END
+}
+
 }  // extern "C"
 
 // ---- accessors used by nccl_merge.cu ------------------------------------------------------------------

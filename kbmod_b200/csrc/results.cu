@@ -414,6 +414,103 @@ void clip_scratch_free(ClipScratch &c) {
     c = ClipScratch();
 }
 
+// ---- near-duplicate grid filter (filters/clustering_grid.py:13-176) -------------------------------
+// The reference hashes every result into a spatial bin (start cell, end cell after max_time) in a Python dict and
+// keeps the best lh per bin (strict '>': the earlier result wins a tie); bins come out in the order they were first
+// seen.  Here: stable sort by lh descending, then four stable sorts by the bin coordinates, so every bin is one run
+// whose head is its winner; the bins are then ordered by the smallest original index they contain.
+__global__ void grid_bins_kernel(const kb_trajectory *__restrict__ list, uint64_t n, double bin_width, double max_time,
+                                 int f32_product, int4 *__restrict__ bins, uint32_t *keys, uint32_t *vals) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const kb_trajectory t = list[i];
+    // add_trajectory (clustering_grid.py:72-75): python doubles.  add_trajectory_list (:109-113): numpy, where
+    // max_time * vx stays float32 before it is added to the integer column.
+    const double ex = f32_product ? (double)__fmul_rn((float)max_time, t.vx) : __dmul_rn(max_time, (double)t.vx);
+    const double ey = f32_product ? (double)__fmul_rn((float)max_time, t.vy) : __dmul_rn(max_time, (double)t.vy);
+    int4 b;
+    b.x = (int)__ddiv_rn((double)t.x, bin_width);                       // int(): truncation toward zero
+    b.y = (int)__ddiv_rn((double)t.y, bin_width);
+    b.z = (int)__ddiv_rn(__dadd_rn((double)t.x, ex), bin_width);
+    b.w = (int)__ddiv_rn(__dadd_rn((double)t.y, ey), bin_width);
+    bins[i] = b;
+    keys[i] = lh_key(t.lh == 0.0f ? 0.0f : t.lh);   // -0.0 and +0.0 compare equal in the reference
+    vals[i] = (uint32_t)i;
+}
+__global__ void grid_comp_kernel(const int4 *__restrict__ bins, const uint32_t *__restrict__ order, int comp, uint64_t n,
+                                 uint32_t *__restrict__ keys) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    keys[i] = reinterpret_cast<const uint32_t *>(bins + order[i])[comp];
+}
+__device__ __forceinline__ bool grid_is_head(const int4 *bins, const uint32_t *order, uint64_t i) {
+    if (i == 0) return true;
+    const int4 a = bins[order[i]], b = bins[order[i - 1]];
+    return a.x != b.x || a.y != b.y || a.z != b.z || a.w != b.w;
+}
+__global__ void grid_flag_kernel(const int4 *__restrict__ bins, const uint32_t *__restrict__ order, uint64_t n,
+                                 uint32_t *__restrict__ flags) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = grid_is_head(bins, order, i) ? 1u : 0u;
+}
+__global__ void grid_segment_kernel(const int4 *__restrict__ bins, const uint32_t *__restrict__ order,
+                                    const uint32_t *__restrict__ excl, uint64_t n, uint32_t *seg_first,
+                                    uint32_t *seg_best) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const bool head = grid_is_head(bins, order, i);
+    const uint32_t seg = excl[i] + (head ? 1u : 0u) - 1u;
+    atomicMin(seg_first + seg, order[i]);
+    if (head) seg_best[seg] = order[i];
+}
+
+int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time, int f32_product,
+                        uint32_t *d_idx_out, uint64_t *n_out, ResultScratch &scr, cudaStream_t st) {
+    *n_out = 0;
+    if (n == 0) return 0;
+    if (n >= (1ull << 31)) throw Error("Too many trajectories for the grid filter.");
+    ensure_scratch(scr, n, 1);
+    int4 *bins = nullptr;
+    uint32_t *flags = nullptr, *total = nullptr;
+    KB_CUDA(cudaMalloc(&bins, sizeof(int4) * n));
+    KB_CUDA(cudaMalloc(&flags, sizeof(uint32_t) * n));
+    KB_CUDA(cudaMalloc(&total, sizeof(uint32_t)));
+    int launches = 0;
+    try {
+        const unsigned gs = (unsigned)((n + 255) / 256);
+        grid_bins_kernel<<<gs, 256, 0, st>>>(d_list, n, bin_width, max_time, f32_product, bins, scr.keys[0], scr.vals[0]);
+        launches += 1 + radix_sort_pairs(scr, n, st);
+        for (int comp = 3; comp >= 0; --comp) {
+            grid_comp_kernel<<<gs, 256, 0, st>>>(bins, scr.vals[0], comp, n, scr.keys[0]);
+            launches += 1 + radix_sort_pairs(scr, n, st);
+        }
+        grid_flag_kernel<<<gs, 256, 0, st>>>(bins, scr.vals[0], n, flags);
+        scan_kernel<<<1, 1024, 0, st>>>(flags, n, total);
+        uint32_t n_seg = 0;
+        KB_CUDA(cudaMemcpyAsync(&n_seg, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        KB_CUDA(cudaStreamSynchronize(st));
+        // keys[1] / vals[1] are free between sorts: first-seen index and winner of every bin
+        KB_CUDA(cudaMemsetAsync(scr.keys[1], 0xff, sizeof(uint32_t) * n_seg, st));
+        grid_segment_kernel<<<gs, 256, 0, st>>>(bins, scr.vals[0], flags, n, scr.keys[1], scr.vals[1]);
+        KB_CUDA(cudaMemcpyAsync(scr.keys[0], scr.keys[1], sizeof(uint32_t) * n_seg, cudaMemcpyDeviceToDevice, st));
+        KB_CUDA(cudaMemcpyAsync(scr.vals[0], scr.vals[1], sizeof(uint32_t) * n_seg, cudaMemcpyDeviceToDevice, st));
+        launches += 3 + radix_sort_pairs(scr, n_seg, st);
+        KB_CUDA(cudaMemcpyAsync(d_idx_out, scr.vals[0], sizeof(uint32_t) * n_seg, cudaMemcpyDeviceToDevice, st));
+        KB_CUDA(cudaStreamSynchronize(st));
+        KB_CUDA(cudaGetLastError());
+        *n_out = n_seg;
+    } catch (...) {
+        cudaFree(bins);
+        cudaFree(flags);
+        cudaFree(total);
+        throw;
+    }
+    cudaFree(bins);
+    cudaFree(flags);
+    cudaFree(total);
+    return launches;
+}
+
 // ---- sorting a trajectory list without allocating anything ----------------------------------------------------
 // The scratch the radix sort needs (two key buffers, two index buffers, the digit histograms and a staging copy of
 // the list) lives in one file-scope device array instead of cudaMalloc'd buffers.  Every GPU that loads this

@@ -381,9 +381,11 @@ __global__ void __launch_bounds__(256)
     const int sw = p.x_start_max - p.x_start_min;
     const int lane = threadIdx.x & 31;
     const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
-    for (unsigned long long i = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n;
-         i += nwarps) {
-        const uint2 it = queue[i];
+    const unsigned long long i0 = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    uint2 nxt = (i0 < n) ? queue[i0] : make_uint2(0u, 0u);
+    for (unsigned long long i = i0; i < n; i += nwarps) {
+        const uint2 it = nxt;
+        if (i + nwarps < n) nxt = queue[i + nwarps];  // in flight while this request is clipped
         const int x = p.x_start_min + (int)(it.x % (unsigned)sw), y = p.y_start_min + (int)(it.x / (unsigned)sw);
         const int c = (int)it.y;
         float lh = -1.0f, flux = -1.0f;  // what the reference keeps when there is no valid observation at all

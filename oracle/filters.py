@@ -234,3 +234,25 @@ def coadds_for_results(sci, var, times, x, y, vx, vy, radius, obs_valid=None):
         out["median"][r] = coadd_median(st)
         out["weighted"][r] = coadd_weighted(st, vs)
     return out
+
+
+# ---- near-duplicate grid filter (filters/clustering_grid.py) --------------------------------------
+def grid_filter_indices(x, y, vx, vy, lh, bin_width, max_time, vectorised=False):
+    """Indices kept by TrajectoryClusterGrid: best lh per (start bin, end bin), strict '>' so the earlier of two equal
+    trajectories stays, bins in first-seen order.  ``vectorised`` follows add_trajectory_list (clustering_grid.py:
+    109-113: max_time * vx is a float32 product), otherwise add_trajectory (:72-75: python doubles)."""
+    table, order = {}, []
+    for i in range(len(x)):
+        xi, yi = int(x[i]), int(y[i])
+        if vectorised:
+            ex = float(np.float32(max_time) * np.float32(vx[i]))
+            ey = float(np.float32(max_time) * np.float32(vy[i]))
+        else:
+            ex, ey = max_time * float(vx[i]), max_time * float(vy[i])
+        key = (int(xi / bin_width), int(yi / bin_width), int((xi + ex) / bin_width), int((yi + ey) / bin_width))
+        if key not in table:
+            table[key] = i
+            order.append(key)
+        elif float(lh[i]) > float(lh[table[key]]):
+            table[key] = i
+    return np.array([table[k] for k in order], dtype=np.int64)
