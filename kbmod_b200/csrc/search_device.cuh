@@ -186,29 +186,55 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     n_valid = n;
     // kernels.cu:201-203: too few observations (or none) -> the clip is skipped; the caller decides what that means
     if (n < min_obs || n == 0) return;
-    // rank[e] = position of my element in ascending order (ties: earlier image first)
+    // rank[e] = position of my element in ascending order (ties: earlier image first).
+    // Fast pass: count the strictly smaller and the equal values (invalid observations travel as NaN, which
+    // compares false both ways).  Without equal values -- the usual case -- the count of smaller ones is the rank.
     int rank[E];
     bool has_tie = false;
+    {
+        float lcs[E];
+        int n_eq[E];
 #pragma unroll
-    for (int e = 0; e < E; ++e) rank[e] = 0;
+        for (int e = 0; e < E; ++e) {
+            lcs[e] = ok[e] ? lc[e] : KB_NAN_F;
+            rank[e] = 0;
+            n_eq[e] = 0;
+        }
 #pragma unroll
-    for (int es = 0; es < E; ++es) {
-        unsigned m = okm[es];
-        while (m) {
-            const int ls = __ffs(m) - 1;
-            m &= m - 1;
-            const float v = __shfl_sync(FULL, lc[es], ls);
-            const int ts = es * 32 + ls;
+        for (int es = 0; es < E; ++es) {
+            const int nsrc = min(32, sv.T - es * 32);  // warp-uniform
+#pragma unroll 4
+            for (int ls = 0; ls < nsrc; ++ls) {
+                const float v = __shfl_sync(FULL, lcs[es], ls);
 #pragma unroll
-            for (int e = 0; e < E; ++e) {
-                const int t = e * 32 + lane;
-                const bool eq = (v == lc[e]);
-                if (v < lc[e] || (eq && ts < t)) rank[e] += 1;
-                has_tie |= ok[e] && eq && ts != t;
+                for (int e = 0; e < E; ++e) {
+                    rank[e] += (v < lcs[e]) ? 1 : 0;
+                    n_eq[e] += (v == lcs[e]) ? 1 : 0;
+                }
             }
         }
+#pragma unroll
+        for (int e = 0; e < E; ++e) has_tie |= ok[e] && n_eq[e] > 1;
     }
     if (__any_sync(FULL, has_tie)) {
+        // Slow pass: ranks with the tie rule, then the payload check below.
+#pragma unroll
+        for (int e = 0; e < E; ++e) rank[e] = 0;
+#pragma unroll
+        for (int es = 0; es < E; ++es) {
+            unsigned m = okm[es];
+            while (m) {
+                const int ls = __ffs(m) - 1;
+                m &= m - 1;
+                const float v = __shfl_sync(FULL, lc[es], ls);
+                const int ts = es * 32 + ls;
+#pragma unroll
+                for (int e = 0; e < E; ++e) {
+                    const int t = e * 32 + lane;
+                    if (v < lc[e] || (v == lc[e] && ts < t)) rank[e] += 1;
+                }
+            }
+        }
         // Equal lc values: harmless when the tied observations carry identical (psi, phi); otherwise the
         // reference's tie order matters for the rounding of the sums and the serial routine must decide.
         bool tie_bad = false;
