@@ -83,6 +83,10 @@ struct kb_stack_s {
     ClipScratch clip;
     kb_timing timing{};
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    // pipelined upload (search_all on a stack that is not preloaded): copy stream, per-chunk events, band streams
+    int zm_known = -1;  // zero_marker decided by an earlier upload of this (immutable) stack; -1 = not yet
+    cudaStream_t copy_stream = nullptr;
+    UploadProgress up;
 };
 
 static size_t pair_bytes(int nb) { return 2 * (size_t)nb; }
@@ -248,6 +252,14 @@ static void destroy_handle(kb_handle h) {
     clip_scratch_free(h->clip);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_stop) cudaEventDestroy(h->ev_stop);
+    for (int i = 0; i < UploadProgress::kMaxChunks; ++i)
+        if (h->up.ev[i]) cudaEventDestroy(h->up.ev[i]);
+    for (int i = 0; i < 2; ++i) {
+        if (h->up.band_done[i]) cudaEventDestroy(h->up.band_done[i]);
+        if (h->up.band_stream[i]) cudaStreamDestroy(h->up.band_stream[i]);
+    }
+    if (h->up.ready) cudaEventDestroy(h->up.ready);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -273,8 +285,65 @@ static void upload_stack(kb_handle h) {
         KB_CUDA(cudaStreamSynchronize(h->stream));
         h->zero_marker = flag ? 0 : 1;
     }
+    h->zm_known = h->zero_marker;
     launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, h->stream);
     h->on_gpu = true;
+}
+
+// The same upload in row chunks on a second stream, so a search can start on the rows that have arrived
+// (launch_search_tiled with an UploadProgress).  Needs the zero-marker decision of an earlier upload: the host copy
+// never changes after construction, so the decision holds.  Returns false when it cannot be used.
+static bool upload_stack_pipelined(kb_handle h) {
+    if (getenv("KB_DEBUG"))
+        fprintf(stderr, "[kbmod_b200] pipelined upload? on_gpu=%d zm_known=%d pinned=%d\n", (int)h->on_gpu, h->zm_known,
+                (int)h->host_pinned);
+    if (h->on_gpu || h->zm_known < 0 || !h->host_pinned) return false;
+    const char *off = getenv("KB_NO_PIPELINED_UPLOAD");
+    if (off && off[0] == '1') return false;
+    const size_t pb = pair_bytes(h->nb);
+    const size_t rows = (size_t)h->T * h->H;
+    const size_t bytes = rows * h->W * pb;
+    size_t min_bytes = 64u << 20;  // small stacks: one copy is as fast
+    if (const char *mb = getenv("KB_PIPELINED_UPLOAD_MIN_BYTES")) min_bytes = (size_t)strtoull(mb, nullptr, 10);
+    if (getenv("KB_DEBUG"))
+        fprintf(stderr, "[kbmod_b200] pipelined upload: %zu bytes (min %zu), H=%d\n", bytes, min_bytes, h->H);
+    if (bytes < min_bytes || h->H < 2 * UploadProgress::kMaxChunks) return false;
+    if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
+    UploadProgress &up = h->up;
+    if (!h->copy_stream) {
+        KB_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < UploadProgress::kMaxChunks; ++i) KB_CUDA(cudaEventCreateWithFlags(&up.ev[i], cudaEventDisableTiming));
+        for (int i = 0; i < 2; ++i) {
+            KB_CUDA(cudaStreamCreateWithFlags(&up.band_stream[i], cudaStreamNonBlocking));
+            KB_CUDA(cudaEventCreateWithFlags(&up.band_done[i], cudaEventDisableTiming));
+        }
+        KB_CUDA(cudaEventCreateWithFlags(&up.ready, cudaEventDisableTiming));
+    }
+    // the copy stream starts after whatever the handle's stream did to the old copy
+    KB_CUDA(cudaEventRecord(up.ready, h->stream));
+    KB_CUDA(cudaStreamWaitEvent(h->copy_stream, up.ready, 0));
+    KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->copy_stream));
+    h->zero_marker = h->zm_known;
+    up.n_chunks = UploadProgress::kMaxChunks;
+    for (int c = 0; c < up.n_chunks; ++c) {
+        const int r0 = (int)((int64_t)h->H * c / up.n_chunks), r1 = (int)((int64_t)h->H * (c + 1) / up.n_chunks);
+        cudaMemcpy3DParms q;
+        memset(&q, 0, sizeof(q));
+        q.srcPtr = make_cudaPitchedPtr(h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, (size_t)h->H);
+        q.dstPtr = make_cudaPitchedPtr(h->d_search, (size_t)h->Wp * pb, (size_t)h->Wp * pb, (size_t)h->H);
+        q.srcPos = make_cudaPos(0, (size_t)r0, 0);
+        q.dstPos = make_cudaPos(0, (size_t)r0, 0);
+        q.extent = make_cudaExtent((size_t)h->W * pb, (size_t)(r1 - r0), (size_t)h->T);
+        q.kind = cudaMemcpyHostToDevice;
+        KB_CUDA(cudaMemcpy3DAsync(&q, h->copy_stream));
+        launch_canonicalise_rows(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0,
+                                 r1 - r0, h->copy_stream);
+        up.row_end[c] = r1;
+        KB_CUDA(cudaEventRecord(up.ev[c], h->copy_stream));
+    }
+    h->on_gpu = true;
+    return true;
 }
 
 static void check_params(kb_handle h, const kb_params *p) {
@@ -558,7 +627,14 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_total.start(st);
     const bool was_on_gpu = h->on_gpu;
     t_h2d.start(st);
-    if (!was_on_gpu) { upload_stack(h); launches += 1; }
+    // Not preloaded: the stack comes up for this search only.  From the second search of a handle on, in row chunks
+    // on a copy stream, and the tiled kernel follows the rows as they land.
+    bool pipelined = false;
+    if (!was_on_gpu) {
+        if (h->kernel_mode != 1) pipelined = upload_stack_pipelined(h);
+        if (!pipelined) upload_stack(h);
+        launches += pipelined ? 2 * UploadProgress::kMaxChunks - 1 : 1;
+    }
     t_h2d.stop(st);
 
     t_prep.start(st);
@@ -573,7 +649,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     TiledPlan *plan = nullptr;
     std::string why;
     if (h->kernel_mode != 1) {
-        plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why);
+        plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data());
         if (!plan && h->kernel_mode == 2) throw Error("tiled kernel not usable: " + why);
         if (!plan && getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] generic kernel used: %s\n", why.c_str());
     }
@@ -582,7 +658,11 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_search.start(st);
     uint32_t sl = 0;
     try {
-        if (plan) sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st);
+        if (pipelined && !plan)  // the generic kernel reads any row: wait for the whole stack
+            KB_CUDA(cudaStreamWaitEvent(st, h->up.ev[h->up.n_chunks - 1], 0));
+        if (plan)
+            sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st,
+                                     pipelined ? &h->up : nullptr);
         else sl = launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
     } catch (...) {
         if (plan) tiled_plan_destroy(plan);

@@ -108,10 +108,23 @@ int merge_clip_survivors(const ClipSurvivor *d_surv, uint64_t n, Slot *d_slots, 
 // search_tiled.cu
 struct TiledPlan;  // opaque: schedule for the TMA-staged kernel
 // Returns nullptr (and a reason) when the tiled kernel cannot be used for this search.
+// h_times: host copy of the T image times (avoids a device read-back while an upload is in flight).
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
-                             uint64_t n_cand, cudaStream_t st, std::string *why_not);
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times = nullptr);
+// A stack upload in flight on another stream: rows [0, row_end[c]) of every image are on the device (and
+// canonical) once ev[c] has fired.  With it, launch_search_tiled starts on the rows that have arrived: the frame is
+// searched in row bands, each waiting only for the chunk that completes its reach.
+struct UploadProgress {
+    static constexpr int kMaxChunks = 8;
+    int n_chunks = 0;
+    int row_end[kMaxChunks] = {0};
+    cudaEvent_t ev[kMaxChunks] = {nullptr};
+    cudaStream_t band_stream[2] = {nullptr, nullptr};
+    cudaEvent_t band_done[2] = {nullptr, nullptr}, ready = nullptr;
+};
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
-                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st);
+                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st,
+                        const UploadProgress *up = nullptr);
 void tiled_plan_destroy(TiledPlan *plan);
 float tiled_plan_kernel_ms(TiledPlan *plan);  // duration of the gather kernel of the last launch (CUDA events)
 
@@ -130,6 +143,8 @@ int launch_encode(const float2 *d_pairs, uint64_t n, int nb, const float psi_p[3
 // rows of `src_pitch` pixel pairs -> canonical search copy with pitch Wp (in place when src == dst and pitches match).
 int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
                         int zero_marker, cudaStream_t st);
+int launch_canonicalise_rows(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
+                             int zero_marker, int r0, int nr, cudaStream_t st);
 // float stacks: sets *d_flag to 1 when some valid pair is exactly (0, 0) (then the zero marker cannot be used).
 int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int H, int W, uint32_t *d_flag,
                                    cudaStream_t st);

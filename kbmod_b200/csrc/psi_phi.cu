@@ -274,30 +274,36 @@ __device__ __forceinline__ ushort2 invalid_pair<ushort2>() { return make_ushort2
 template <>
 __device__ __forceinline__ uchar2 invalid_pair<uchar2>() { return make_uchar2(0, 0); }
 
+// The kernels below visit rows [r0, r0 + nr) of each of the T images of H rows (the whole stack: r0 = 0, nr = H).
+__device__ __forceinline__ uint64_t stack_row(uint64_t r, int H, int r0, int nr) {
+    return (r / (uint64_t)nr) * (uint64_t)H + (uint64_t)r0 + r % (uint64_t)nr;
+}
+
 template <typename T2>
-__global__ void canonicalise_kernel(const T2 *src, int src_pitch, T2 *dst, uint64_t rows, int W, int Wp) {
-    const uint64_t total = rows * (uint64_t)Wp;
+__global__ void canonicalise_kernel(const T2 *src, int src_pitch, T2 *dst, int T, int H, int r0, int nr, int W, int Wp) {
+    const uint64_t total = (uint64_t)T * nr * (uint64_t)Wp;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t r = i / Wp;
+        const uint64_t g = stack_row(i / Wp, H, r0, nr);
         const int c = (int)(i % Wp);
-        dst[i] = (c < W) ? canon(src[r * src_pitch + c]) : invalid_pair<T2>();  // padding columns: invalid
+        dst[g * Wp + c] = (c < W) ? canon(src[g * src_pitch + c]) : invalid_pair<T2>();  // padding columns: invalid
     }
 }
 
 // float stacks, zero-marker form: invalid -> (+0, +0)
-__global__ void canonicalise_zero_kernel(const float2 *src, int src_pitch, float2 *dst, uint64_t rows, int W, int Wp) {
-    const uint64_t total = rows * (uint64_t)Wp;
+__global__ void canonicalise_zero_kernel(const float2 *src, int src_pitch, float2 *dst, int T, int H, int r0, int nr,
+                                         int W, int Wp) {
+    const uint64_t total = (uint64_t)T * nr * (uint64_t)Wp;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t r = i / Wp;
+        const uint64_t g = stack_row(i / Wp, H, r0, nr);
         const int c = (int)(i % Wp);
         float2 v = make_float2(0.0f, 0.0f);
         if (c < W) {
-            const float2 s = src[r * src_pitch + c];
+            const float2 s = src[g * src_pitch + c];
             if (isfinite(s.x) && isfinite(s.y)) v = s;
         }
-        dst[i] = v;
+        dst[g * Wp + c] = v;
     }
 }
 
@@ -319,20 +325,24 @@ int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int 
     KB_CUDA(cudaGetLastError());
     return 1;
 }
-int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
-                        int zero_marker, cudaStream_t st) {
+int launch_canonicalise_rows(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
+                             int zero_marker, int r0, int nr, cudaStream_t st) {
     if (d_src == d_dst && src_pitch != Wp) throw Error("in-place canonicalise needs equal pitches");
-    const uint64_t rows = (uint64_t)T * H;
+    if (nr <= 0) return 0;
     if (nb == 4 && zero_marker)
-        canonicalise_zero_kernel<<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, rows, W, Wp);
+        canonicalise_zero_kernel<<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, T, H, r0, nr, W, Wp);
     else if (nb == 4)
-        canonicalise_kernel<float2><<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, rows, W, Wp);
+        canonicalise_kernel<float2><<<148 * 8, 256, 0, st>>>((const float2 *)d_src, src_pitch, (float2 *)d_dst, T, H, r0, nr, W, Wp);
     else if (nb == 2)
-        canonicalise_kernel<ushort2><<<148 * 8, 256, 0, st>>>((const ushort2 *)d_src, src_pitch, (ushort2 *)d_dst, rows, W, Wp);
+        canonicalise_kernel<ushort2><<<148 * 8, 256, 0, st>>>((const ushort2 *)d_src, src_pitch, (ushort2 *)d_dst, T, H, r0, nr, W, Wp);
     else
-        canonicalise_kernel<uchar2><<<148 * 8, 256, 0, st>>>((const uchar2 *)d_src, src_pitch, (uchar2 *)d_dst, rows, W, Wp);
+        canonicalise_kernel<uchar2><<<148 * 8, 256, 0, st>>>((const uchar2 *)d_src, src_pitch, (uchar2 *)d_dst, T, H, r0, nr, W, Wp);
     KB_CUDA(cudaGetLastError());
     return 1;
+}
+int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
+                        int zero_marker, cudaStream_t st) {
+    return launch_canonicalise_rows(d_src, src_pitch, d_dst, T, H, W, Wp, nb, zero_marker, 0, H, st);
 }
 
 }  // namespace kb

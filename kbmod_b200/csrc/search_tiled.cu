@@ -86,7 +86,7 @@ static bool decode_is_exact_in_fp32(int nb, float scale, float mn) {
 }
 
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
-                             uint64_t n_cand, cudaStream_t st, std::string *why_not) {
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times) {
     auto no = [&](const char *why) -> TiledPlan * {
         if (why_not) *why_not = why;
         return nullptr;
@@ -102,8 +102,12 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             return no("fp32 decode would not be bit-exact for this scale/offset");
     }
     std::vector<double> times(T);
-    KB_CUDA(cudaMemcpyAsync(times.data(), sv.times, sizeof(double) * T, cudaMemcpyDeviceToHost, st));
-    KB_CUDA(cudaStreamSynchronize(st));
+    if (h_times) {
+        std::copy(h_times, h_times + T, times.begin());
+    } else {
+        KB_CUDA(cudaMemcpyAsync(times.data(), sv.times, sizeof(double) * T, cudaMemcpyDeviceToHost, st));
+        KB_CUDA(cudaStreamSynchronize(st));
+    }
     double tabs = 0.0;
     for (double t : times) {
         if (!std::isfinite(t)) return no("non-finite time");
@@ -214,6 +218,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int max_ch = rmax / TCH;
 
     // ---- stage records, group by group (greedy packing of consecutive images into <= STAGE_BYTES) ---------------
+    std::vector<int> group_reach(std::max(n_groups, 1), 0);
     std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
     std::vector<int> cand((size_t)std::max(n_groups, 1) * TG, -1);
     bool overflow = false;
@@ -254,6 +259,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
             if (nt == 0) t0 = t;
             cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 16), used);
+            group_reach[g] = std::max(group_reach[g], mny + rows_pad);
             for (int j = 0; j < TG; ++j)
                 cur.offs[nt][j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
             used += bytes;
@@ -310,6 +316,13 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     v.clip_cnt = nullptr;
     v.clip_cap = 0;
     plan->smem = (size_t)TS * (STAGE_BYTES + HDR_BYTES) + 2 * TS * 8 + sizeof(double) * (size_t)T;
+    // Rows a tile can touch below its origin: the deepest box bottom of any group; candidates evaluated per pixel
+    // (exact list, winners in the epilogue, clips) go as far as their own last offset.
+    int reach_hi = TBY;
+    for (int r : group_reach) reach_hi = std::max(reach_hi, r);
+    for (int c : exact) reach_hi = std::max(reach_hi, TBY + (int)ceil(fabs((double)h_vy[c]) * tabs) + 2);
+    plan->reach_hi = reach_hi;
+    v.pixel_base = 0;
 
     // ---- tensor maps over the search copy: dims (x elements, rows, images), one per box width ------------------
     const bool f32 = sv.nb == 4;
@@ -349,8 +362,22 @@ void tiled_plan_destroy(TiledPlan *plan) {
     delete plan;
 }
 
+static void launch_tiled_any(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
+                             const float *d_vy, Slot *d_slots, cudaStream_t st) {
+    const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
+    dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
+    switch (sv.nb) {
+        case 4: launch_tiled_nb4(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 2: launch_tiled_nb2(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        case 1: launch_tiled_nb1(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
+        default: throw Error("bad num_bytes");
+    }
+    KB_CUDA(cudaGetLastError());
+}
+
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
-                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st) {
+                        const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st,
+                        const UploadProgress *up) {
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
     if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
@@ -386,15 +413,47 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         KB_CUDA(cudaEventCreate(&plan->ev1));
     }
     KB_CUDA(cudaEventRecord(plan->ev0, st));
-    switch (sv.nb) {
-        case 4: launch_tiled_nb4(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
-        case 2: launch_tiled_nb2(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
-        case 1: launch_tiled_nb1(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
-        default: throw Error("bad num_bytes");
+    int launches = 0;
+    if (!up || up->n_chunks <= 1) {
+        if (up && up->n_chunks == 1) KB_CUDA(cudaStreamWaitEvent(st, up->ev[0], 0));
+        plan->v.pixel_base = 0;
+        launch_tiled_any(plan, sv, p, d_vx, d_vy, d_slots, st);
+        launches = 1;
+    } else {
+        // The stack is still arriving: search row bands as their rows land.  Band b ends where a tile's reach stays
+        // inside the rows of chunk b; bands alternate between two streams so one band's tail overlaps the next.
+        KB_CUDA(cudaEventRecord(up->ready, st));  // candidates, counters, slots are ordered before the bands
+        bool used[2] = {false, false};
+        int ya = p.y_start_min, nb_launched = 0;
+        for (int b = 0; b < up->n_chunks; ++b) {
+            const bool last = (b == up->n_chunks - 1);
+            int yb = last ? p.y_start_max : std::min(p.y_start_max, up->row_end[b] - plan->reach_hi);
+            if (!last && yb > ya) yb = ya + (yb - ya) / TBY * TBY;  // whole tiles, so the tiling equals one launch's
+            if (yb <= ya) continue;
+            kb_params pb = p;
+            pb.y_start_min = ya;
+            pb.y_start_max = yb;
+            const int k = nb_launched & 1;
+            cudaStream_t bs = up->band_stream[k];
+            KB_CUDA(cudaStreamWaitEvent(bs, up->ready, 0));
+            KB_CUDA(cudaStreamWaitEvent(bs, up->ev[b], 0));
+            const size_t row_off = (size_t)(ya - p.y_start_min) * sw;
+            plan->v.pixel_base = (unsigned)row_off;
+            launch_tiled_any(plan, sv, pb, d_vx, d_vy, d_slots + row_off * p.results_per_pixel, bs);
+            used[k] = true;
+            ++nb_launched;
+            ++launches;
+            ya = yb;
+        }
+        plan->v.pixel_base = 0;
+        for (int k = 0; k < 2; ++k)
+            if (used[k]) {
+                KB_CUDA(cudaEventRecord(up->band_done[k], up->band_stream[k]));
+                KB_CUDA(cudaStreamWaitEvent(st, up->band_done[k], 0));
+            }
+        KB_CUDA(cudaStreamWaitEvent(st, up->ev[up->n_chunks - 1], 0));  // clips and the epilogue read any row
     }
-    KB_CUDA(cudaGetLastError());
     KB_CUDA(cudaEventRecord(plan->ev1, st));
-    int launches = 1;
     if (plan->sigmag) {
         unsigned long long cnt[4];
         for (int attempt = 0; attempt < 2; ++attempt) {

@@ -46,6 +46,7 @@ struct PlanView {
     uint2 *clipq;                   // deferred sigma-G requests {start-pixel index, candidate}
     unsigned long long *clip_cnt;  // [0] requests, [1] survivors, [2] clipped in line (queue full)
     unsigned long long clip_cap;
+    unsigned pixel_base;            // start-pixel index of this launch's first pixel within the whole search area
 };
 
 struct TiledPlan {
@@ -54,6 +55,7 @@ struct TiledPlan {
     void *d_block = nullptr;  // one allocation holding all tables
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the gather kernel
     size_t smem = 0;
+    int reach_hi = 0;  // a tile at row y0 reads stack rows below y0 + reach_hi (largest box bottom, padded)
     int nb = 4, K = 8;
     bool sigmag = false;
 };
@@ -216,7 +218,7 @@ __global__ void __launch_bounds__(TNT, 1)
         // ===================== consumer warps: gather, reduce, rank ========================================
         const int px = tile_x0 + lane, py = tile_y0 + warp;
         const bool in_bounds = (px - p.x_start_min) < sw && (py - p.y_start_min) < sh;
-        const unsigned pixel_index = (unsigned)((py - p.y_start_min) * sw + (px - p.x_start_min));
+        const unsigned pixel_index = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px - p.x_start_min));
         float psi[TG], phi[TG];
         int cnt[COUNT ? TG : 1];
         TopK<K> top;
