@@ -270,10 +270,12 @@ def run_ours(args, c, cfg_name):
     if comm is not None:
         comm.barrier()
     d2h = 0
+    h2d = 0
     t0 = time.perf_counter()
     s.timer_start()
     for _ in range(e2e_steps):
-        step()
+        tm = step()
+        h2d = tm["h2d_stack_bytes"]   # the rows this rank's band can reach (the whole stack for a full-frame search)
         res = s.get_results_array()
         d2h = res.nbytes
     ms_e2e_dev = s.timer_stop()
@@ -332,7 +334,7 @@ def run_ours(args, c, cfg_name):
                        "parallelism": f"start-pixel row bands x{world}, psi/phi replicated, NCCL all-gather merge"
                        if world > 1 else "single GPU", "results": int(n_results), "ctor_seconds": ctor_s},
             "roofline": roofline,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(stack_bytes + 8 * len(vx)),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d + 8 * len(vx)),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e, "steps": e2e_steps},
             "gpu_launches": int(launches), "clocks": clocks}
 

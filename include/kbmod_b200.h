@@ -63,6 +63,7 @@ typedef struct {
     uint32_t total_launches;  /* all kernels launched by the call */
     uint32_t used_tiled;      /* 1 when the TMA-staged tiled kernel ran, 0 for the generic kernel */
     float ms_main_kernel;     /* the single gather kernel launch alone (search_tiled_kernel / search_generic_kernel) */
+    uint64_t h2d_stack_bytes; /* psi/phi bytes copied host -> device inside the call (0 when the stack was resident) */
 } kb_timing;
 
 typedef struct kb_stack_s *kb_handle;

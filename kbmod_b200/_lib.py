@@ -37,7 +37,7 @@ class KbTiming(C.Structure):
     _fields_ = [("ms_h2d", C.c_float), ("ms_prepare", C.c_float), ("ms_search", C.c_float),
                 ("ms_filter_sort", C.c_float), ("ms_total", C.c_float), ("evals", C.c_uint64),
                 ("search_launches", C.c_uint32), ("total_launches", C.c_uint32), ("used_tiled", C.c_uint32),
-                ("ms_main_kernel", C.c_float)]
+                ("ms_main_kernel", C.c_float), ("h2d_stack_bytes", C.c_uint64)]
 
 
 # numpy view of kb_trajectory (common.h:55-67; 28 bytes)

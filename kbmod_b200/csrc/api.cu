@@ -293,7 +293,7 @@ static void upload_stack(kb_handle h) {
 // The same upload in row chunks on a second stream, so a search can start on the rows that have arrived
 // (launch_search_tiled with an UploadProgress).  Needs the zero-marker decision of an earlier upload: the host copy
 // never changes after construction, so the decision holds.  Returns false when it cannot be used.
-static bool upload_stack_pipelined(kb_handle h) {
+static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t *bytes_copied) {
     if (getenv("KB_DEBUG"))
         fprintf(stderr, "[kbmod_b200] pipelined upload? on_gpu=%d zm_known=%d pinned=%d\n", (int)h->on_gpu, h->zm_known,
                 (int)h->host_pinned);
@@ -308,6 +308,15 @@ static bool upload_stack_pipelined(kb_handle h) {
     if (getenv("KB_DEBUG"))
         fprintf(stderr, "[kbmod_b200] pipelined upload: %zu bytes (min %zu), H=%d\n", bytes, min_bytes, h->H);
     if (bytes < min_bytes || h->H < 2 * UploadProgress::kMaxChunks) return false;
+    // Only the rows this search can touch (its start rows plus the candidates' reach) are brought up: the copy is
+    // dropped again after the search, so the rest of the stack is never read.  Too thin a range: take everything.
+    row_lo = std::max(0, std::min(row_lo, h->H));
+    row_hi = std::max(0, std::min(row_hi, h->H));
+    if (row_hi - row_lo < 2 * UploadProgress::kMaxChunks) {
+        row_lo = 0;
+        row_hi = h->H;
+    }
+    const int64_t span = row_hi - row_lo;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     UploadProgress &up = h->up;
@@ -324,10 +333,12 @@ static bool upload_stack_pipelined(kb_handle h) {
     KB_CUDA(cudaEventRecord(up.ready, h->stream));
     KB_CUDA(cudaStreamWaitEvent(h->copy_stream, up.ready, 0));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->copy_stream));
+    if (const char *poison = getenv("KB_POISON_STACK"))  // tests: rows that are not uploaded must never be read
+        if (poison[0] == '1') KB_CUDA(cudaMemsetAsync(h->d_search, 0xA5, rows * h->Wp * pb, h->copy_stream));
     h->zero_marker = h->zm_known;
     up.n_chunks = UploadProgress::kMaxChunks;
     for (int c = 0; c < up.n_chunks; ++c) {
-        const int r0 = (int)((int64_t)h->H * c / up.n_chunks), r1 = (int)((int64_t)h->H * (c + 1) / up.n_chunks);
+        const int r0 = row_lo + (int)(span * c / up.n_chunks), r1 = row_lo + (int)(span * (c + 1) / up.n_chunks);
         cudaMemcpy3DParms q;
         memset(&q, 0, sizeof(q));
         q.srcPtr = make_cudaPitchedPtr(h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, (size_t)h->H);
@@ -343,6 +354,7 @@ static bool upload_stack_pipelined(kb_handle h) {
         KB_CUDA(cudaEventRecord(up.ev[c], h->copy_stream));
     }
     h->on_gpu = true;
+    if (bytes_copied) *bytes_copied = (uint64_t)span * h->T * h->W * pb;
     return true;
 }
 
@@ -631,8 +643,18 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     // on a copy stream, and the tiled kernel follows the rows as they land.
     bool pipelined = false;
     if (!was_on_gpu) {
-        if (h->kernel_mode != 1) pipelined = upload_stack_pipelined(h);
+        uint64_t copied = h->meta.total_array_size;
+        if (h->kernel_mode != 1) {
+            // rows within reach of the start rows: |vy| * max|t| plus a tile, its padding and a margin
+            double vmax = 0.0, tabs = 0.0;
+            for (uint64_t i = 0; i < n_cand; ++i) vmax = std::max(vmax, (double)fabsf(vy[i]));
+            for (double t : h->times) tabs = std::max(tabs, fabs(t));
+            const double reach_d = std::min(vmax * tabs + 64.0, 4.0e6);
+            const int reach = (int)reach_d;
+            pipelined = upload_stack_pipelined(h, p.y_start_min - reach, p.y_start_max + reach, &copied);
+        }
         if (!pipelined) upload_stack(h);
+        h->timing.h2d_stack_bytes = copied;
         launches += pipelined ? 2 * UploadProgress::kMaxChunks - 1 : 1;
     }
     t_h2d.stop(st);
