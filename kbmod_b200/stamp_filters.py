@@ -2,7 +2,7 @@
 (filters/stamp_filters.py:72-160) over ``kbmod.core.stamp_utils`` (extract_stamp_stack, coadd_sum / coadd_mean /
 coadd_median / coadd_weighted, core/stamp_utils.py:16-349), through ``kb_coadd_stamps`` (csrc/stamps.cu).
 
-No CPU path.  Results are float32 ``R x S x S`` arrays (S = 2 * radius + 1), bit-identical to the reference's.
+No CPU path.  Per-night coadds (``nightly=True``) are one device pass per calendar day.  Results are float32 ``R x S x S`` arrays (S = 2 * radius + 1), bit-identical to the reference's.
 """
 import ctypes as C
 
@@ -65,11 +65,25 @@ def append_coadds(result_data, im_stack, coadd_types, radius, valid_only=True, n
     ``var``, ``zeroed_times``)."""
     if radius <= 0:
         raise ValueError(f"Invalid stamp radius {radius}")
-    if nightly:
-        raise RuntimeError("kbmod_b200: per-night coadds are not built (nightly=False only)")
     valid_only = valid_only and "obs_valid" in result_data.colnames
-    ov = np.asarray(result_data["obs_valid"]) if valid_only else None
-    co = coadd_stamps(im_stack.sci, im_stack.var, im_stack.zeroed_times, result_data["x"], result_data["y"],
-                      result_data["vx"], result_data["vy"], radius, tuple(coadd_types), ov)
-    for t, a in co.items():
+    ov = np.asarray(result_data["obs_valid"], dtype=bool) if valid_only else None
+    args = (im_stack.sci, im_stack.var, im_stack.zeroed_times, result_data["x"], result_data["y"],
+            result_data["vx"], result_data["vy"], radius, tuple(coadd_types))
+    for t, a in coadd_stamps(*args, ov).items():
         result_data.table[f"coadd_{t}"] = a
+    if nightly:
+        # one more set of coadds per calendar day (stamp_filters.py:101-106,151-168): the images of that day only
+        day_strs = np.array([f"_{mjd_to_day(t)}" for t in im_stack.times])
+        num_res = len(result_data["x"])
+        for day in np.unique(day_strs):
+            day_mask = np.broadcast_to(day_strs == day, (num_res, len(day_strs)))
+            mask = day_mask if ov is None else (ov & day_mask)
+            for t, a in coadd_stamps(*args, mask).items():
+                result_data.table[f"coadd_{t}{day}"] = a
+
+
+def mjd_to_day(mjd):
+    """util_functions.py:52-65 without astropy: the UTC calendar date (YYYY-MM-DD) of a modified Julian date."""
+    import datetime
+    import math
+    return (datetime.date(1858, 11, 17) + datetime.timedelta(days=math.floor(float(mjd)))).strftime("%Y-%m-%d")

@@ -112,5 +112,16 @@ def test_gpu_append_coadds_on_search_results():
     want = of.coadds_for_results(case["sci"], case["var"], case["times"], tab["x"], tab["y"], tab["vx"], tab["vy"], 4, ov)
     for k in TYPES:
         assert same_f32(tab[f"coadd_{k}"], want[k]), k
-    with pytest.raises(RuntimeError):
-        append_coadds(tab, stack, ["sum"], 4, nightly=True)
+    # per-night coadds: one column per calendar day, built from that day's valid images only
+    stack.times = 60000.25 + np.asarray(case["times"])
+    append_coadds(tab, stack, ["sum", "median"], 4, nightly=True)
+    from kbmod_b200.stamp_filters import mjd_to_day
+    assert mjd_to_day(60000) == "2023-02-25"           # util_functions.py:63
+    days = sorted({mjd_to_day(t) for t in stack.times})
+    assert len(days) >= 2
+    total = np.zeros_like(tab["coadd_sum"], dtype=np.float64)
+    for d in days:
+        day_mask = np.array([mjd_to_day(t) == d for t in stack.times])
+        want_d = of.coadds_for_results(case["sci"], case["var"], case["times"], tab["x"], tab["y"], tab["vx"], tab["vy"], 4,
+                                       ov & day_mask[None, :])
+        assert same_f32(tab[f"coadd_sum_{d}"], want_d["sum"]) and same_f32(tab[f"coadd_median_{d}"], want_d["median"])
