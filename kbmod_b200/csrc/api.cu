@@ -638,6 +638,20 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
 
     t_total.start(st);
     const bool was_on_gpu = h->on_gpu;
+    // A stack brought up for this search only (possibly just the rows in reach) must not outlive the call, also
+    // when the call fails half way.
+    struct DropTransientStack {
+        kb_handle h;
+        bool active;
+        ~DropTransientStack() {
+            if (!active) return;
+            cudaStreamSynchronize(h->stream);
+            if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+            for (int i = 0; i < 2; ++i)
+                if (h->up.band_stream[i]) cudaStreamSynchronize(h->up.band_stream[i]);
+            free_device_stack(h, true);
+        }
+    } drop{h, !was_on_gpu};
     t_h2d.start(st);
     // Not preloaded: the stack comes up for this search only.  From the second search of a handle on, in row chunks
     // on a copy stream, and the tiled kernel follows the rows as they land.
@@ -719,7 +733,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     h->timing.ms_filter_sort = t_post.ms();
     h->timing.ms_total = t_total.ms();
     h->timing.total_launches = launches;
-    if (!was_on_gpu) free_device_stack(h, true);  // search_all drops the stack again unless preloaded (:257)
+    // search_all drops the stack again unless preloaded (:257): `drop` does it on every way out of this function
     if (invalid) throw Error("Invalid trajectory detected in the search results.");
     if (n_results) *n_results = n_keep;
     KB_API_END
