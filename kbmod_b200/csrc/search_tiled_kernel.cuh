@@ -263,7 +263,18 @@ __global__ void __launch_bounds__(TNT, 1)
                         if (ZM) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
-                            if (COUNT && ok) cnt[j] += 1;
+                            if (COUNT && NB == 4) {
+                                // valid <=> the pair is not (+-0, +-0): one LOP3 with a predicate result and one
+                                // predicated add in place (the compiler's select form costs two more per gather)
+                                asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+                                    "lop3.b32 t, %1, 0x7fffffff, %2, 0xc8;\n\t"
+                                    "setp.ne.u32 p, t, 0;\n\t"
+                                    "@p add.s32 %0, %0, 1;\n\t}"
+                                    : "+r"(cnt[j])
+                                    : "r"(__float_as_uint(a)), "r"(__float_as_uint(b)));
+                            } else if (COUNT && ok) {
+                                cnt[j] += 1;
+                            }
                         } else if (ok) {
                             psi[j] = __fadd_rn(psi[j], a);
                             phi[j] = __fadd_rn(phi[j], b);
