@@ -10,7 +10,7 @@ from .search import array_to_trajectories, trajectories_to_array
 
 
 def _grid_indices(arr, bin_width, max_time, f32_product):
-    require_gpu()
+    require_gpu()   # after the callers' argument checks
     idx = np.zeros(max(arr.size, 1), dtype=np.uint32)
     n = C.c_uint64(0)
     check(lib.kb_grid_filter(ptr(arr), C.c_uint64(arr.size), C.c_double(bin_width), C.c_double(max_time),

@@ -21,7 +21,6 @@ def coadd_stamps(sci, var, zeroed_times, x, y, vx, vy, radius, coadd_types=COADD
     """Coadds for R trajectories.  ``sci`` / ``var``: T images (list or T x H x W array); ``x, y, vx, vy``: length-R
     arrays (the float64 columns of the reference's result table); ``obs_valid``: optional R x T booleans selecting the
     images of each trajectory (``valid_only``).  Returns {type: float32[R, S, S]}."""
-    require_gpu()
     if radius <= 0:
         raise ValueError(f"Invalid stamp radius {radius}")
     for t in coadd_types:
@@ -51,6 +50,7 @@ def coadd_stamps(sci, var, zeroed_times, x, y, vx, vy, radius, coadd_types=COADD
             raise ValueError("Wrong shape for obs_valid")
     S = 2 * radius + 1
     out = {t: np.zeros((R, S, S), dtype=np.float32) for t in coadd_types}
+    require_gpu()
     if R:
         check(lib.kb_coadd_stamps(ptr_array(sci), ptr_array(var) if need_var else None, C.c_int(T), C.c_int(H), C.c_int(W),
                                   ptr(times), ptr(x), ptr(y), ptr(vx), ptr(vy), C.c_uint64(R), C.c_int(radius),

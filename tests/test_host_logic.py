@@ -85,3 +85,28 @@ def test_compute_calls_fail_loudly_without_gpu():
         kb.StackSearch([img], [img + 1], [np.ones((1, 1), np.float32)], [0.0])
     with pytest.raises(RuntimeError):
         kb.search_cpu_only(None, None, None, None)
+
+
+def test_post_search_mirrors_validate_before_touching_the_gpu():
+    """Argument errors of the filter / stamp mirrors are the reference's (ValueError) and need no device."""
+    import numpy as np
+    from kbmod_b200.clustering_grid import TrajectoryClusterGrid, apply_trajectory_grid_filter
+    from kbmod_b200.sigma_g_filter import SigmaGClipping
+    from kbmod_b200.stamp_filters import coadd_stamps, mjd_to_day
+    for bad in [(0, 1.0), (10, -1.0), (float("inf"), 1.0)]:
+        with pytest.raises(ValueError):
+            TrajectoryClusterGrid(*bad)
+        with pytest.raises(ValueError):
+            apply_trajectory_grid_filter([], *bad)
+    with pytest.raises(ValueError):
+        SigmaGClipping(low_bnd=80, high_bnd=20)
+    img = [np.zeros((8, 8), np.float32)] * 3
+    with pytest.raises(ValueError):
+        coadd_stamps(img, img, [0.0, 1.0, 2.0], [1], [1], [0.0], [0.0], 0)
+    with pytest.raises(ValueError):
+        coadd_stamps(img, img, [0.0, 1.0, 2.0], [1], [1], [0.0], [0.0], 2, ("mode",))
+    with pytest.raises(ValueError):
+        coadd_stamps(img, img, [0.0, 1.0], [1], [1], [0.0], [0.0], 2)          # one time per image
+    with pytest.raises(ValueError):
+        coadd_stamps(img, img, [0.0, 1.0, 2.0], [1, 2], [1], [0.0], [0.0], 2)   # ragged trajectory columns
+    assert mjd_to_day(60000) == "2023-02-25" and mjd_to_day(60000.99) == "2023-02-25"
