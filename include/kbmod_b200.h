@@ -187,6 +187,12 @@ KB_EXPORT int kb_coadd_stamps(const float *const *sci, const float *const *var, 
                               const double *vy, uint64_t n, int radius, const uint8_t *obs_valid, float *out_sum,
                               float *out_mean, float *out_median, float *out_weighted);
 
+/* append_all_stamps (filters/stamp_filters.py:163-211) over extract_stamp_stack (core/stamp_utils.py:16-84,352-439):
+ * out is n x T x S x S float32, the stamp of every trajectory at every image, NaN where there is no image. */
+KB_EXPORT int kb_extract_stamps(const float *const *sci, int T, int H, int W, const double *times, const double *x0,
+                                const double *y0, const double *vx, const double *vy, uint64_t n, int radius,
+                                float *out);
+
 /* ---- measurement hooks (no reference counterpart) ---------------------------------------------------- */
 /* CUDA events recorded on the handle's own stream, so a caller can time a region of calls on the device:
  * kb_timer_start records the start event; kb_timer_stop records the stop event, waits for it and returns the

@@ -120,6 +120,25 @@ __global__ void __launch_bounds__(kStampThreads)
     }
 }
 
+// append_all_stamps (filters/stamp_filters.py:163-211): every stamp of every result, T x S x S per result, NaN where
+// there is no image.  One thread per output pixel.
+__global__ void all_stamps_kernel(const float *__restrict__ sci, int T, int H, int W, const double *__restrict__ times,
+                                  const double *__restrict__ x0, const double *__restrict__ y0,
+                                  const double *__restrict__ vx, const double *__restrict__ vy, uint64_t n, int radius,
+                                  float *__restrict__ out) {
+    const int S = 2 * radius + 1;
+    const uint64_t per = (uint64_t)T * S * S, total = n * per;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / per;
+        const int rem = (int)(i % per), t = rem / (S * S), p = rem % (S * S);
+        const long long x = (long long)stamp_center(vx[r], times[t], x0[r]) + (p % S - radius);
+        const long long y = (long long)stamp_center(vy[r], times[t], y0[r]) + (p / S - radius);
+        float v = KB_NAN_F;
+        if (x >= 0 && x < W && y >= 0 && y < H) v = sci[(size_t)t * H * W + (size_t)y * W + x];
+        out[i] = v;
+    }
+}
+
 namespace {
 struct DBuf {
     void *p = nullptr;
@@ -182,5 +201,38 @@ extern "C" KB_EXPORT int kb_coadd_stamps(const float *const *sci, const float *c
     if (out_mean) KB_CUDA(cudaMemcpy(out_mean, d_mean.p, ob, cudaMemcpyDeviceToHost));
     if (out_median) KB_CUDA(cudaMemcpy(out_median, d_med.p, ob, cudaMemcpyDeviceToHost));
     if (out_weighted) KB_CUDA(cudaMemcpy(out_weighted, d_w.p, ob, cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
+extern "C" KB_EXPORT int kb_extract_stamps(const float *const *sci, int T, int H, int W, const double *times,
+                                           const double *x0, const double *y0, const double *vx, const double *vy,
+                                           uint64_t n, int radius, float *out) {
+    KB_API_BEGIN
+    int dev_count = 0;
+    if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0)
+        throw Error("no CUDA device: kbmod_b200 has no CPU path");
+    if (radius < 1) throw Error("Invalid stamp radius: " + std::to_string(radius));
+    if (radius > 255) throw Error("stamp radius above 255 is not supported");
+    if (T <= 0 || H <= 0 || W <= 0) throw Error("empty image stack");
+    if (n == 0) return 0;
+    if (!sci || !times || !x0 || !y0 || !vx || !vy || !out) throw Error("null argument");
+    const int S = 2 * radius + 1;
+    const size_t img = (size_t)H * W;
+    const uint64_t total = n * (uint64_t)T * S * S;
+    if (total >= (1ull << 36)) throw Error("too many stamp pixels for one call");
+    DBuf d_sci(img * T * 4), d_t(8 * (size_t)T), d_par(4 * 8 * n), d_out(total * 4);
+    for (int t = 0; t < T; ++t)
+        KB_CUDA(cudaMemcpy(d_sci.as<float>() + img * t, sci[t], img * 4, cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(d_t.p, times, 8 * (size_t)T, cudaMemcpyHostToDevice));
+    double *par = d_par.as<double>();
+    KB_CUDA(cudaMemcpy(par, x0, 8 * n, cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(par + n, y0, 8 * n, cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(par + 2 * n, vx, 8 * n, cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(par + 3 * n, vy, 8 * n, cudaMemcpyHostToDevice));
+    const unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, 148ull * 32);
+    all_stamps_kernel<<<grid, 256>>>(d_sci.as<float>(), T, H, W, d_t.as<double>(), par, par + n, par + 2 * n, par + 3 * n,
+                                     n, radius, d_out.as<float>());
+    KB_CUDA(cudaGetLastError());
+    KB_CUDA(cudaMemcpy(out, d_out.p, total * 4, cudaMemcpyDeviceToHost));
     KB_API_END
 }

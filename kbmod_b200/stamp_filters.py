@@ -59,6 +59,41 @@ def coadd_stamps(sci, var, zeroed_times, x, y, vx, vy, radius, coadd_types=COADD
     return out
 
 
+def extract_all_stamps(sci, zeroed_times, x, y, vx, vy, radius):
+    """Every stamp of every trajectory: float32 ``R x T x S x S``, NaN where there is no image
+    (extract_stamp_stack, core/stamp_utils.py:16-84, for all results at once)."""
+    if radius < 1:
+        raise ValueError(f"Invalid stamp radius: {radius}")
+    sci = [f32(a) for a in sci]
+    T = len(sci)
+    if T == 0:
+        raise ValueError("empty image stack")
+    H, W = sci[0].shape
+    times = _f64(zeroed_times)
+    if times.shape != (T,):
+        raise ValueError("one time per image is required")
+    x, y, vx, vy = _f64(x), _f64(y), _f64(vx), _f64(vy)
+    R = x.size
+    if not (y.size == R and vx.size == R and vy.size == R):
+        raise ValueError("x, y, vx, vy must have the same length")
+    S = 2 * radius + 1
+    out = np.zeros((R, T, S, S), dtype=np.float32)
+    require_gpu()
+    if R:
+        check(lib.kb_extract_stamps(ptr_array(sci), C.c_int(T), C.c_int(H), C.c_int(W), ptr(times), ptr(x), ptr(y),
+                                    ptr(vx), ptr(vy), C.c_uint64(R), C.c_int(radius), ptr(out)))
+    return out
+
+
+def append_all_stamps(result_data, im_stack, stamp_radius):
+    """filters/stamp_filters.py:163-211: the ``all_stamps`` column (R x T x S x S float32)."""
+    if stamp_radius < 1:
+        raise ValueError(f"Invalid stamp radius: {stamp_radius}")
+    result_data.table["all_stamps"] = extract_all_stamps(im_stack.sci, im_stack.zeroed_times, result_data["x"],
+                                                         result_data["y"], result_data["vx"], result_data["vy"],
+                                                         stamp_radius)
+
+
 def append_coadds(result_data, im_stack, coadd_types, radius, valid_only=True, nightly=False):
     """filters/stamp_filters.py:72-160 for a reference ``Results``-like table (columns x, y, vx, vy[, obs_valid]; new
     columns are written through ``result_data.table[name] = array``) and an ``ImageStackPy``-like stack (``sci``,

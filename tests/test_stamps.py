@@ -125,3 +125,27 @@ def test_gpu_append_coadds_on_search_results():
         want_d = of.coadds_for_results(case["sci"], case["var"], case["times"], tab["x"], tab["y"], tab["vx"], tab["vy"], 4,
                                        ov & day_mask[None, :])
         assert same_f32(tab[f"coadd_sum_{d}"], want_d["sum"]) and same_f32(tab[f"coadd_median_{d}"], want_d["median"])
+
+
+@pytest.mark.gpu
+def test_gpu_all_stamps(golden):
+    from kbmod_b200.stamp_filters import append_all_stamps, extract_all_stamps
+    g = golden
+    radius = int(g["radius"])
+    got = extract_all_stamps(g["sci"], g["times"], g["x"], g["y"], g["vx"], g["vy"], radius)
+    assert got.shape == (len(g["x"]), len(g["times"]), 2 * radius + 1, 2 * radius + 1) and got.dtype == np.float32
+    assert same_f32(got[2], g["all_stamps_r2"])                      # the reference's own extract_stamp_stack
+    xs = of.stamp_positions(g["times"], g["x"], g["vx"])
+    ys = of.stamp_positions(g["times"], g["y"], g["vy"])
+    for r in range(len(g["x"])):
+        assert same_f32(got[r], of.extract_stamp_stack(list(g["sci"]), xs[r], ys[r], radius).astype(np.float32)), r
+    assert np.isnan(got[0]).all()                                     # trajectory 0 never touches the image
+
+    class Table(dict):
+        table = property(lambda self: self)
+    tab = Table(x=g["x"], y=g["y"], vx=g["vx"], vy=g["vy"])
+    stack = type("Stack", (), dict(sci=list(g["sci"]), zeroed_times=g["times"]))()
+    append_all_stamps(tab, stack, radius)
+    assert same_f32(tab["all_stamps"], got)
+    with pytest.raises(ValueError):
+        append_all_stamps(tab, stack, 0)
