@@ -32,9 +32,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE search-kernel launch from an `ncu --set full` capture of this
-# workload (profiles/r01_ncu_search_tiled_raw.csv: 4.186 GB read + 0.942 GB written; the algorithmic gather
+# workload (profiles/r01_ncu_search_tiled_raw.csv: 4.146 GB read + 0.941 GB written; the algorithmic gather
 # bytes of the same launch are 1342 GB, the stack itself is 0.671 GB).
-NCU_DRAM_BYTES_PER_LAUNCH = {("C2", True): 5.13e9}
+NCU_DRAM_BYTES_PER_LAUNCH = {("C2", True): 5.09e9}
 
 METRIC = "pixel-trajectory-obs evals/sec"
 UNIT = "evals/s"

@@ -669,7 +669,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
         }
         if (!pipelined) upload_stack(h);
         h->timing.h2d_stack_bytes = copied;
-        launches += pipelined ? 2 * UploadProgress::kMaxChunks - 1 : 1;
+        launches += pipelined ? UploadProgress::kMaxChunks : (h->nb == 4 ? 2 : 1);  // canonicalise (+ zero detection) kernels
     }
     t_h2d.stop(st);
 
