@@ -48,6 +48,39 @@ class TrajectoryClusterGrid:
     def __len__(self):
         return len(self._solve())
 
+    def _keys(self):
+        """Bin key of every collected trajectory (host arithmetic identical to the device's, clustering_grid.py:72-75
+        for add_trajectory, :109-113 for add_trajectory_list)."""
+        keys = []
+        for trj, f32 in zip(self._trjs, self._f32):
+            if f32:
+                ex = float(np.float32(self.max_time) * np.float32(trj.vx))
+                ey = float(np.float32(self.max_time) * np.float32(trj.vy))
+            else:
+                ex, ey = self.max_time * trj.vx, self.max_time * trj.vy
+            keys.append((int(trj.x / self.bin_width), int(trj.y / self.bin_width),
+                         int((trj.x + ex) / self.bin_width), int((trj.y + ey) / self.bin_width)))
+        return keys
+
+    @property
+    def table(self):
+        """{bin key: best trajectory}, bins in first-seen order (the reference's ``table`` dict)."""
+        keys = self._keys()
+        return {keys[i]: self._trjs[i] for i in self._solve()}
+
+    @property
+    def idx_table(self):
+        keys = self._keys()
+        return {keys[i]: self._idx[i] for i in self._solve()}
+
+    @property
+    def count(self):
+        """{bin key: number of trajectories that fell into the bin}."""
+        out = {}
+        for k in self._keys():
+            out[k] = out.get(k, 0) + 1
+        return out
+
     def add_trajectory(self, trj, idx=None):
         if idx is None:
             idx = self.total_count
