@@ -79,3 +79,24 @@ def test_gpu_grid_filter_large_and_errors():
             apply_trajectory_grid_filter(arr[:5], *bad)
         with pytest.raises(ValueError):
             TrajectoryClusterGrid(*bad)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/kbmod/filters"), reason="reference sources not present")
+def test_oracle_matches_reference_live():
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    import make_golden_grid as mg
+    from oracle import ref as oref
+    if not oref.available():
+        pytest.skip("oracle/_ref not built")
+    mod, S = mg.load_reference_grid()
+    rng = np.random.default_rng(77)
+    for trial, (bw, mt) in enumerate([(10, 1.0), (3, 7.7), (16.5, 0.3)]):
+        x, y, vx, vy, lh = mg.make_trajectories(rng, 500)
+        trjs = [S.Trajectory(x=int(a), y=int(b), vx=float(c), vy=float(d), lh=float(e), flux=1.0, obs_count=10)
+                for a, b, c, d, e in zip(x, y, vx, vy, lh)]
+        _, idx = mod.apply_trajectory_grid_filter(trjs, bw, mt)
+        assert np.array_equal(of.grid_filter_indices(x, y, vx, vy, lh, bw, mt), np.array(idx)), trial
+        g = mod.TrajectoryClusterGrid(bin_width=bw, max_time=mt)
+        g.add_trajectory_list(trjs)
+        assert np.array_equal(of.grid_filter_indices(x, y, vx, vy, lh, bw, mt, True), np.array(g.get_indices())), trial

@@ -149,3 +149,36 @@ def test_gpu_all_stamps(golden):
     assert same_f32(tab["all_stamps"], got)
     with pytest.raises(ValueError):
         append_all_stamps(tab, stack, 0)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/kbmod/core"), reason="reference sources not present")
+def test_oracle_matches_reference_live():
+    """Random stacks through the reference's own stamp_utils functions (loaded as in make_golden_stamps.py)."""
+    import sys
+    import warnings
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    import make_golden_stamps as mg
+    su = mg.load_reference_stamp_utils()
+    rng = np.random.default_rng(31)
+    for trial in range(4):
+        T, H, W, radius = int(rng.integers(1, 9)), 17, 13, int(rng.integers(1, 5))
+        sci = rng.normal(0, 3, (T, H, W)).astype(np.float32)
+        var = (1 + rng.random((T, H, W))).astype(np.float32)
+        sci[rng.random((T, H, W)) < 0.15] = np.nan
+        var[rng.random((T, H, W)) < 0.05] = 0.0
+        times = np.sort(rng.random(T) * 4)
+        x, y = rng.integers(-4, W + 4, 6).astype(float), rng.integers(-4, H + 4, 6).astype(float)
+        vx, vy = rng.uniform(-3, 3, 6), rng.uniform(-3, 3, 6)
+        inc = rng.random((6, T)) < 0.7
+        xs, ys = mg.reference_positions(times, x, vx), mg.reference_positions(times, y, vy)
+        assert np.array_equal(xs, of.stamp_positions(times, x, vx)) and np.array_equal(ys, of.stamp_positions(times, y, vy))
+        want = of.coadds_for_results(list(sci), list(var), times, x, y, vx, vy, radius, inc)
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            for r in range(6):
+                s = np.asanyarray(su.extract_stamp_stack(sci, xs[r], ys[r], radius, to_include=inc[r]))
+                v = np.asanyarray(su.extract_stamp_stack(var, xs[r], ys[r], radius, to_include=inc[r]))
+                assert same_f32(want["sum"][r], su.coadd_sum(s).astype(np.float32))
+                assert same_f32(want["mean"][r], su.coadd_mean(s).astype(np.float32))
+                assert same_f32(want["median"][r], su.coadd_median(s, device="cpu").astype(np.float32))
+                assert same_f32(want["weighted"][r], su.coadd_weighted(s, v).astype(np.float32))
