@@ -211,8 +211,7 @@ def run_ours(args, c, cfg_name):
     frames = 1 if strong else world            # strong: the named frame itself, start-pixel rows split over the ranks
     stack, vx, vy = make_inputs(c, frames)
     if strong:
-        edges = [round(i * c["H"] / world) for i in range(world + 1)]
-        band = (edges[rank], edges[rank + 1])
+        band = tuple(dist.row_bands(0, c["H"], world)[rank])
         rows = c["H"] / world                  # per-rank average (the job total is what is reported)
     else:
         band = (rank * c["H"], (rank + 1) * c["H"])
