@@ -71,9 +71,31 @@ def workload_name(cfg_name, c, n_gpus):
             + (f", one of {c['band_div']} start-pixel row bands per GPU" if c.get("band_div") else ""))
 
 
+def host_threads():
+    """Host threads this process may run on (its CPU affinity mask, not the machine's core count)."""
+    try:
+        return max(len(os.sched_getaffinity(0)), 1)
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def loaded_native_libraries():
+    """Shared objects of this repository that are mapped into the process (from /proc/self/maps)."""
+    out = set()
+    try:
+        for ln in open("/proc/self/maps"):
+            path = ln.split()[-1] if "/" in ln else ""
+            if path.endswith(".so") and path.startswith(ROOT):
+                out.add(os.path.relpath(path, ROOT))
+    except OSError:
+        pass
+    return sorted(out)
+
+
 def make_inputs(c, n_gpus):
+    # host-only modules: neither loads libkbmod_b200.so, so the reference arm's process never maps our library
     from kbmod_b200 import fake_data as fd
-    from kbmod_b200.search import Trajectory
+    from kbmod_b200.trajectory import Trajectory
     times = fd.create_fake_times(c["T"], 57130.2, obs_per_day=c["obs_per_day"], intra_night_gap=c.get("intra", 0.01))
     ds = fd.FakeDataSet(c["W"], c["H"] * n_gpus, times, mask_fraction=c["mask"], psf_val=c["psf"], use_seed=c["seed"])
     if "grid" in c or "ecliptic" in c:
@@ -147,12 +169,38 @@ def reference_cpu_setup(c, stack, vx, vy, target_seconds):
     """Build the reference StackSearch on a crop of the same synthetic stack and choose a start-pixel window so
     one search_all(use_gpu=False) takes about `target_seconds` on this box's cores."""
     from oracle import ref
-    S, _ = ref.load()
-    cores = os.cpu_count() or 1
+    S, H = ref.load()
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the reference's CPU search is an OpenMP loop and gets every
+    # host thread this process may use.  `cores` is what OpenMP reports afterwards, not a guess.
+    H.set_omp_threads(host_threads())
+    cores = int(H.omp_threads())
     n_cand, T = len(vx), c["T"]
     tmax = float(stack.zeroed_times[-1])
     reach = int(np.ceil(max(np.abs(vx).max(), np.abs(vy).max()) * tmax)) + 1
-    w = int(np.sqrt(max(target_seconds * 3.0e7 * cores / (n_cand * T), 16.0 * 16.0)))
+    # evals/s of the reference on these cores: measured on a small probe window of a small crop, not assumed
+    rate = 3.0e7 * cores
+    try:
+        pside = min(min(c["H"], c["W"]), 48 + 2 * reach)
+        pw = max(8, min(48, pside))
+        plo = max((pside - pw) // 2, 0)
+        ps = S.StackSearch([np.ascontiguousarray(a[:pside, :pside]) for a in stack.sci],
+                           [np.ascontiguousarray(a[:pside, :pside]) for a in stack.var], list(stack.psfs),
+                           [float(t) for t in stack.zeroed_times], c["nb"])
+        ps.set_min_obs(c["min_obs"])
+        ps.set_min_lh(c["min_lh"])
+        ps.set_results_per_pixel(c["K"])
+        ps.set_start_bounds_x(plo, min(plo + pw, pside))
+        ps.set_start_bounds_y(plo, min(plo + pw, pside))
+        pc = [S.Trajectory(vx=float(a), vy=float(b)) for a, b in zip(vx, vy)]
+        pwx = min(plo + pw, pside) - plo
+        ps.search_all(pc, False)
+        t0 = time.perf_counter()
+        ps.search_all(pc, False)
+        rate = max(pwx * pwx * n_cand * T / max(time.perf_counter() - t0, 1e-4), 1e6)
+        del ps
+    except Exception:
+        pass
+    w = int(np.sqrt(max(target_seconds * rate / (n_cand * T), 16.0 * 16.0)))
     w = max(16, min(w, min(c["H"], c["W"]) - 2 * reach if min(c["H"], c["W"]) > 2 * reach + 64 else w))
     side = min(min(c["H"], c["W"]), w + 2 * reach)
     lo = max((side - w) // 2, 0)
@@ -193,7 +241,7 @@ def run_reference(args, c, cfg_name):
             "config": {"workload": workload_name(cfg_name, c, 1), "timed_on": "host cores", "sample": sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "native_so_loaded": loaded_native_libraries()}
     print(json.dumps(line), flush=True)
 
 
@@ -384,6 +432,10 @@ def main():
                          "(BASELINE configs C4 / C5)")
     args = ap.parse_args()
     c = CONFIGS[args.config]
+    # torchrun exports OMP_NUM_THREADS=1; our host code (first touch of the host copy, schedule construction) is
+    # OpenMP too.  Give every rank its share of the host threads before the library (and its libgomp) is loaded.
+    if args.impl == "ours" and os.environ.get("OMP_NUM_THREADS") == "1" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        os.environ["OMP_NUM_THREADS"] = str(max(host_threads() // int(os.environ.get("LOCAL_WORLD_SIZE", os.environ["WORLD_SIZE"])), 1))
     if args.impl == "reference":
         run_reference(args, c, args.config)
     else:

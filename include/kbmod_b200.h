@@ -169,10 +169,10 @@ KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64
 /* TrajectoryClusterGrid / apply_trajectory_grid_filter (filters/clustering_grid.py:13-176): every trajectory falls
  * into the spatial bin (int(x/w), int(y/w), int((x + max_time*vx)/w), int((y + max_time*vy)/w)); idx_out receives,
  * for every occupied bin in the order the bins are first seen, the index of its best trajectory (largest lh; the
- * earlier one wins a tie); *n_out = number of bins.  f32_product != 0 evaluates max_time*v in float32 as the
- * vectorised add_trajectory_list does (:109-113), 0 in double as add_trajectory does (:72-75).  Host pointers;
- * idx_out has room for n entries. */
-KB_EXPORT int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time, int f32_product,
+ * earlier one wins a tie); *n_out = number of bins.  max_time*v is a double product, in add_trajectory (:72-75)
+ * and in the vectorised add_trajectory_list (:109-113) alike (the velocity columns reach numpy as Python floats).
+ * Host pointers; idx_out has room for n entries. */
+KB_EXPORT int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time,
                              uint32_t *idx_out, uint64_t *n_out);
 
 /* ---- coadded stamps of the results ----------------------------------------------------- */

@@ -9,12 +9,12 @@ from ._lib import check, lib, ptr, require_gpu
 from .search import array_to_trajectories, trajectories_to_array
 
 
-def _grid_indices(arr, bin_width, max_time, f32_product):
+def _grid_indices(arr, bin_width, max_time):
     require_gpu()   # after the callers' argument checks
     idx = np.zeros(max(arr.size, 1), dtype=np.uint32)
     n = C.c_uint64(0)
     check(lib.kb_grid_filter(ptr(arr), C.c_uint64(arr.size), C.c_double(bin_width), C.c_double(max_time),
-                             C.c_int(1 if f32_product else 0), ptr(idx), C.byref(n)))
+                             ptr(idx), C.byref(n)))
     return idx[: n.value].astype(np.int64)
 
 
@@ -32,32 +32,23 @@ class TrajectoryClusterGrid:
         self.total_count = 0
         self._trjs = []
         self._idx = []
-        self._f32 = []
         self._cache = None
 
     def _solve(self):
         if self._cache is None:
-            arr = trajectories_to_array(self._trjs)
-            f32 = np.array(self._f32, dtype=bool)
-            if f32.any() and not f32.all():
-                raise RuntimeError("kbmod_b200: do not mix add_trajectory and add_trajectory_list on one grid "
-                                   "(the reference bins them with different arithmetic)")
-            self._cache = _grid_indices(arr, self.bin_width, self.max_time, bool(f32.all()) if len(f32) else False)
+            self._cache = _grid_indices(trajectories_to_array(self._trjs), self.bin_width, self.max_time)
         return self._cache
 
     def __len__(self):
         return len(self._solve())
 
     def _keys(self):
-        """Bin key of every collected trajectory (host arithmetic identical to the device's, clustering_grid.py:72-75
-        for add_trajectory, :109-113 for add_trajectory_list)."""
+        """Bin key of every collected trajectory (host arithmetic identical to the device's: double products in
+        add_trajectory, clustering_grid.py:72-75, and -- the velocity columns being Python floats -- in
+        add_trajectory_list, :109-113)."""
         keys = []
-        for trj, f32 in zip(self._trjs, self._f32):
-            if f32:
-                ex = float(np.float32(self.max_time) * np.float32(trj.vx))
-                ey = float(np.float32(self.max_time) * np.float32(trj.vy))
-            else:
-                ex, ey = self.max_time * trj.vx, self.max_time * trj.vy
+        for trj in self._trjs:
+            ex, ey = self.max_time * trj.vx, self.max_time * trj.vy
             keys.append((int(trj.x / self.bin_width), int(trj.y / self.bin_width),
                          int((trj.x + ex) / self.bin_width), int((trj.y + ey) / self.bin_width)))
         return keys
@@ -86,7 +77,6 @@ class TrajectoryClusterGrid:
             idx = self.total_count
         self._trjs.append(trj)
         self._idx.append(idx)
-        self._f32.append(False)
         self.total_count += 1
         self._cache = None
 
@@ -94,7 +84,6 @@ class TrajectoryClusterGrid:
         for idx, trj in enumerate(trj_list):
             self._trjs.append(trj)
             self._idx.append(idx)
-            self._f32.append(True)
         self.total_count += len(trj_list)
         self._cache = None
 
@@ -112,8 +101,8 @@ def apply_trajectory_grid_filter(trajectories, bin_width, max_dt):
     if max_dt < 0 or not np.isfinite(max_dt):
         raise ValueError(f"Max time must be >= 0. Got {max_dt}.")
     if isinstance(trajectories, np.ndarray):
-        keep = _grid_indices(np.ascontiguousarray(trajectories), bin_width, max_dt, False)
+        keep = _grid_indices(np.ascontiguousarray(trajectories), bin_width, max_dt)
         return trajectories[keep], [int(i) for i in keep]
     trajectories = list(trajectories)
-    keep = _grid_indices(trajectories_to_array(trajectories), bin_width, max_dt, False)
+    keep = _grid_indices(trajectories_to_array(trajectories), bin_width, max_dt)
     return [trajectories[i] for i in keep], [int(i) for i in keep]

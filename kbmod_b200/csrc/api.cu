@@ -892,8 +892,8 @@ int kb_sigmag_filtered_indices(const float *values, int n, float sgl0, float sgl
     KB_API_END
 }
 
-int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time, int f32_product,
-                   uint32_t *idx_out, uint64_t *n_out) {
+int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, double max_time, uint32_t *idx_out,
+                   uint64_t *n_out) {
     KB_API_BEGIN
     if (!n_out) throw Error("null argument");
     *n_out = 0;
@@ -913,7 +913,7 @@ int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, doub
     KB_CUDA(cudaMemcpy(d_list.p, trjs, sizeof(kb_trajectory) * n, cudaMemcpyHostToDevice));
     ResultScratch scr;
     try {
-        grid_filter_indices(d_list.p, n, bin_width, max_time, f32_product, d_idx.p, n_out, scr, 0);
+        grid_filter_indices(d_list.p, n, bin_width, max_time, d_idx.p, n_out, scr, 0);
         KB_CUDA(cudaMemcpy(idx_out, d_idx.p, sizeof(uint32_t) * (*n_out), cudaMemcpyDeviceToHost));
     } catch (...) {
         result_scratch_free(scr);

@@ -162,7 +162,7 @@ struct ResultScratch {
 };
 void result_scratch_free(ResultScratch &s);
 // clustering_grid.py: indices of the best trajectory of every spatial bin, bins in first-seen order.
-int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time, int f32_product,
+int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time,
                         uint32_t *d_idx_out, uint64_t *n_out, ResultScratch &scr, cudaStream_t st);
 // slots[P*K] -> filtered, sorted kb_trajectory list. Two phases so the caller can size the output:
 // filter_count() returns the number of survivors (syncs the stream); filter_finish() writes them to d_out.

@@ -17,9 +17,10 @@ __device__ __forceinline__ bool slot_passes(const Slot &s, float min_lh, int min
     return !(s.lh < min_lh) && !(s.obs < min_obs);  // remove_if(lh < min_lh), remove_if(obs < min_obs)
 }
 
-// key: ascending unsigned order == descending lh
+// key: ascending unsigned order == descending lh.  -0.0 and +0.0 compare equal in the reference's sort, so both map
+// to the key of +0.0 and keep their input order like any other tie.
 __device__ __forceinline__ uint32_t lh_key(float lh) {
-    const uint32_t u = __float_as_uint(lh);
+    const uint32_t u = __float_as_uint(lh == 0.0f ? 0.0f : lh);
     const uint32_t ordered = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
     return ~ordered;
 }
@@ -420,21 +421,22 @@ void clip_scratch_free(ClipScratch &c) {
 // seen.  Here: stable sort by lh descending, then four stable sorts by the bin coordinates, so every bin is one run
 // whose head is its winner; the bins are then ordered by the smallest original index they contain.
 __global__ void grid_bins_kernel(const kb_trajectory *__restrict__ list, uint64_t n, double bin_width, double max_time,
-                                 int f32_product, int4 *__restrict__ bins, uint32_t *keys, uint32_t *vals) {
+                                 int4 *__restrict__ bins, uint32_t *keys, uint32_t *vals) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const kb_trajectory t = list[i];
-    // add_trajectory (clustering_grid.py:72-75): python doubles.  add_trajectory_list (:109-113): numpy, where
-    // max_time * vx stays float32 before it is added to the integer column.
-    const double ex = f32_product ? (double)__fmul_rn((float)max_time, t.vx) : __dmul_rn(max_time, (double)t.vx);
-    const double ey = f32_product ? (double)__fmul_rn((float)max_time, t.vy) : __dmul_rn(max_time, (double)t.vy);
+    // add_trajectory (clustering_grid.py:72-75): python doubles.  add_trajectory_list (:109-113) gets vx/vy from
+    // extract_all_trajectory_vx, a std::vector<float> that pybind11 hands over as a list of Python floats, so numpy
+    // makes it float64: the product max_time * vx is a double product there too.
+    const double ex = __dmul_rn(max_time, (double)t.vx);
+    const double ey = __dmul_rn(max_time, (double)t.vy);
     int4 b;
     b.x = (int)__ddiv_rn((double)t.x, bin_width);                       // int(): truncation toward zero
     b.y = (int)__ddiv_rn((double)t.y, bin_width);
     b.z = (int)__ddiv_rn(__dadd_rn((double)t.x, ex), bin_width);
     b.w = (int)__ddiv_rn(__dadd_rn((double)t.y, ey), bin_width);
     bins[i] = b;
-    keys[i] = lh_key(t.lh == 0.0f ? 0.0f : t.lh);   // -0.0 and +0.0 compare equal in the reference
+    keys[i] = lh_key(t.lh);
     vals[i] = (uint32_t)i;
 }
 __global__ void grid_comp_kernel(const int4 *__restrict__ bins, const uint32_t *__restrict__ order, int comp, uint64_t n,
@@ -464,7 +466,7 @@ __global__ void grid_segment_kernel(const int4 *__restrict__ bins, const uint32_
     if (head) seg_best[seg] = order[i];
 }
 
-int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time, int f32_product,
+int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time,
                         uint32_t *d_idx_out, uint64_t *n_out, ResultScratch &scr, cudaStream_t st) {
     *n_out = 0;
     if (n == 0) return 0;
@@ -478,7 +480,7 @@ int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_widt
     int launches = 0;
     try {
         const unsigned gs = (unsigned)((n + 255) / 256);
-        grid_bins_kernel<<<gs, 256, 0, st>>>(d_list, n, bin_width, max_time, f32_product, bins, scr.keys[0], scr.vals[0]);
+        grid_bins_kernel<<<gs, 256, 0, st>>>(d_list, n, bin_width, max_time, bins, scr.keys[0], scr.vals[0]);
         launches += 1 + radix_sort_pairs(scr, n, st);
         for (int comp = 3; comp >= 0; --comp) {
             grid_comp_kernel<<<gs, 256, 0, st>>>(bins, scr.vals[0], comp, n, scr.keys[0]);

@@ -19,7 +19,7 @@ import math
 
 import numpy as np
 
-from .search import Trajectory
+from .trajectory import Trajectory
 
 
 def create_fake_times(num_times, t0=0.0, obs_per_day=1, intra_night_gap=0.01, inter_night_gap=1):

@@ -239,16 +239,13 @@ def coadds_for_results(sci, var, times, x, y, vx, vy, radius, obs_valid=None):
 # ---- near-duplicate grid filter (filters/clustering_grid.py) --------------------------------------
 def grid_filter_indices(x, y, vx, vy, lh, bin_width, max_time, vectorised=False):
     """Indices kept by TrajectoryClusterGrid: best lh per (start bin, end bin), strict '>' so the earlier of two equal
-    trajectories stays, bins in first-seen order.  ``vectorised`` follows add_trajectory_list (clustering_grid.py:
-    109-113: max_time * vx is a float32 product), otherwise add_trajectory (:72-75: python doubles)."""
+    trajectories stays, bins in first-seen order.  add_trajectory (clustering_grid.py:72-75) multiplies python
+    doubles; so does the ``vectorised`` add_trajectory_list (:109-113), because extract_all_trajectory_vx returns a
+    std::vector<float> that pybind11 turns into a list of Python floats, which numpy makes float64."""
     table, order = {}, []
     for i in range(len(x)):
         xi, yi = int(x[i]), int(y[i])
-        if vectorised:
-            ex = float(np.float32(max_time) * np.float32(vx[i]))
-            ey = float(np.float32(max_time) * np.float32(vy[i]))
-        else:
-            ex, ey = max_time * float(vx[i]), max_time * float(vy[i])
+        ex, ey = max_time * float(vx[i]), max_time * float(vy[i])
         key = (int(xi / bin_width), int(yi / bin_width), int((xi + ex) / bin_width), int((yi + ey) / bin_width))
         if key not in table:
             table[key] = i

@@ -16,6 +16,9 @@
 
 #include <cfloat>
 #include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace refh {
 using search::PsiPhiArray;
@@ -102,6 +105,24 @@ SearchParameters make_params(int min_obs, float min_lh, bool sigmag, float sgl_L
     p.results_per_pixel = K; p.total_results = 0;
     return p;
 }
+
+// OpenMP threads the reference's CPU loops will use (search_cpu_only, cpu_search_algorithms.cpp:96-124, is an
+// `omp parallel for`).  Launchers such as torchrun export OMP_NUM_THREADS=1; the benchmark's reference arm sets
+// and reports the real number through these two.
+int omp_threads() {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+void set_omp_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
 }  // namespace refh
 
 PYBIND11_MODULE(ref_harness, m) {
@@ -109,4 +130,6 @@ PYBIND11_MODULE(ref_harness, m) {
     m.def("eval_host", &refh::eval_host);
     m.def("search_slots", &refh::search_slots);
     m.def("make_params", &refh::make_params);
+    m.def("omp_threads", &refh::omp_threads);
+    m.def("set_omp_threads", &refh::set_omp_threads);
 }

@@ -49,11 +49,17 @@ def main():
     mod, S = load_reference_grid()
     rng = np.random.default_rng(123)
     out = {}
-    cases = [(400, 10, 1.0), (1500, 25, 4.03), (60, 1, 0.0), (300, 7.5, 2.5)]
+    cases = [(400, 10, 1.0), (1500, 25, 4.03), (60, 1, 0.0), (300, 7.5, 2.5), (64, 25, 4.03)]
     out["cases"] = np.array(cases, dtype=np.float64)
     for i, (n, bw, mt) in enumerate(cases):
         n = int(n)
         x, y, vx, vy, lh = make_trajectories(rng, n)
+        if i == 4:
+            # A bin edge that tells a double product from a float32 one: (69 + 4.03 * 7.692307472229004) / 25 is
+            # 3.99999... in double (bin 3) and 4.0 when 4.03 * vx is rounded to float32 first (bin 4).
+            x[:2], y[:2], vx[:2], vy[:2] = 69, 10, np.float32(7.692307472229004), 0.0
+            x[1] = 70
+            lh[:2] = (20.0, 30.0)
         trjs = [S.Trajectory(x=int(a), y=int(b), vx=float(c), vy=float(d), lh=float(e), flux=1.0, obs_count=10)
                 for a, b, c, d, e in zip(x, y, vx, vy, lh)]
         bw_arg = int(bw) if float(bw).is_integer() else bw

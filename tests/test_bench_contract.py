@@ -13,8 +13,11 @@ def test_reference_arm_prints_one_contract_line():
     from oracle import ref as oref
     if not oref.available():
         pytest.skip("oracle/_ref (the reference build) is not present")
+    # torchrun hands its workers OMP_NUM_THREADS=1: the arm must still use, and report, every host thread it may run on
+    env = dict(os.environ, OMP_NUM_THREADS="1")
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--config", "C1",
-                          "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=300, cwd=ROOT)
+                          "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=300, cwd=ROOT,
+                         env=env)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
     assert len(lines) == 1, out.stdout
@@ -24,7 +27,10 @@ def test_reference_arm_prints_one_contract_line():
     assert d["vs_baseline"] is None and d["data"] == "synthetic" and d["gpu_launches"] == 0
     assert d["config"]["workload"].startswith("C1:")
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    assert cb["kind"] == "reference" and cb["value"] == d["value"] and cb["sample"]
+    assert cb["cores"] == len(os.sched_getaffinity(0)) and f"{cb['cores']} host threads" in cb["sample"]
+    # the arm times the reference build only: our CUDA library is never mapped into that process
+    assert d["native_so_loaded"] and all("libkbmod_b200" not in p for p in d["native_so_loaded"])
     assert d["e2e"] == {"value": d["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
