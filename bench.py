@@ -31,11 +31,6 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE search-kernel launch from an `ncu --set full` capture of this
-# workload (profiles/r01_ncu_search_tiled_raw.csv: 4.146 GB read + 0.941 GB written; the algorithmic gather
-# bytes of the same launch are 1342 GB, the stack itself is 0.671 GB).
-NCU_DRAM_BYTES_PER_LAUNCH = {("C2", True): 5.09e9}
-
 METRIC = "pixel-trajectory-obs evals/sec"
 UNIT = "evals/s"
 
@@ -245,6 +240,88 @@ def run_reference(args, c, cfg_name):
     print(json.dumps(line), flush=True)
 
 
+def measure_peaks():
+    """Roofline denominators measured on this device, in this process (kb_measure_peaks), in GB/s."""
+    import ctypes as C
+    from kbmod_b200._lib import check, lib
+    buf = (C.c_double * 6)()
+    check(lib.kb_measure_peaks(buf, C.c_int(6)))
+    names = ("hbm_stream_read", "l2_resident_read", "l2_row_gather_256B", "smem_lds64", "smem_lds32", "smem_lds16")
+    return dict(zip(names, [float(v) for v in buf]))
+
+
+def results_digest(arr):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(arr).view(np.uint8).tobytes()).hexdigest()[:16]
+
+
+def reference_gpu_leg(c, stack, vx, vy):
+    """The checker, outside every timed region of our arm: the UNMODIFIED reference's own CUDA search_all from
+    oracle/_ref on this GPU, same workload.  Returns (parity record, timing record).  Parity is taken on the pair of
+    stacks both sides can build bit-identically (science images convolved beforehand + a 1x1 PSF: the reference's
+    FFMA-contracted GPU convolution then equals its CPU convolution, which is what we reproduce)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity import assert_lists_equal_modulo_ties
+    from kbmod_b200 import search as kb
+    from kbmod_b200._lib import TRAJECTORY_DTYPE
+    from oracle import cpu as orc, ref as oref
+    S, Hn = oref.load()
+    if not S.kb_has_gpu():
+        raise RuntimeError("the reference build sees no GPU")
+    T, H, W = c["T"], c["H"], c["W"]
+    times = [float(t) for t in stack.zeroed_times]
+    sci = [kb.convolve_image(np.ascontiguousarray(a, dtype=np.float32), p) for a, p in zip(stack.sci, stack.psfs)]
+    one = [np.ones((1, 1), dtype=np.float32)] * T
+    var = list(stack.var)
+    evals = H * W * len(vx) * T
+    ss = S.StackSearch(sci, var, one, times, c["nb"])
+    configure(ss, c)
+    cands = [S.Trajectory(vx=float(a), vy=float(b)) for a, b in zip(vx, vy)]
+    t0 = time.perf_counter()
+    ss.search_all(cands, True)                       # uploads psi/phi inside the call, like our e2e leg
+    ref_e2e_ms = 1e3 * (time.perf_counter() - t0)
+    ss.preload_psi_phi_array()
+    ref_ms = []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        ss.search_all(cands, True)
+        ref_ms.append(1e3 * (time.perf_counter() - t0))
+    n = ss.get_number_total_results()
+    want = np.zeros(n, dtype=TRAJECTORY_DTYPE)
+    if n:
+        lst = ss.get_results(0, n)
+        for f in ("x", "y", "vx", "vy", "lh", "flux", "obs_count"):
+            want[f] = getattr(S, "extract_all_trajectory_" + f)(lst)
+    ss.unload_psi_phi_array()
+    s = kb.StackSearch(sci, var, one, times, c["nb"])
+    configure(s, c)
+    s.search_all((vx, vy), True)
+    got = s.get_results_array()
+    arr = s.psi_phi_array
+    ra = S.PsiPhiArray()
+    S.fill_psi_phi_array_from_image_arrays(ra, c["nb"], sci, var, one, times)
+    same_bytes = bool(np.array_equal(Hn.psi_phi_bytes(ra), arr.host_array().view(np.uint8).ravel()))
+    del ra, ss
+    nb = arr.num_bytes
+    pp = (arr.psi_min_val, arr.psi_max_val, arr.psi_scale) if nb != 4 else (0, 0, 1)
+    fp = (arr.phi_min_val, arr.phi_max_val, arr.phi_scale) if nb != 4 else (0, 0, 1)
+    ost = orc.PsiPhiStack(arr.host_array(), stack.zeroed_times, T, H, W, nb, pp, fp)
+    prm = orc.make_params(c["min_obs"], c["min_lh"], (0.25, 0.75, 0.7413) if c["sigmag"] else None, None, c["K"], ost)
+    parity = {"vs": "reference_gpu", "what": "oracle/_ref StackSearch.search_all(candidates, True), full frame, same GPU",
+              "psi_phi_bytes_identical": same_bytes, "n": int(len(got)), "n_reference": int(len(want))}
+    try:
+        assert_lists_equal_modulo_ties(got, want, orc, ost, prm, "bench parity leg")
+        parity["identical_modulo_ties"] = bool(same_bytes)
+    except AssertionError as e:
+        parity["identical_modulo_ties"] = False
+        parity["mismatch"] = str(e)[:300]
+    timing = {"ms_per_search": min(ref_ms), "value": evals / (min(ref_ms) * 1e-3), "unit": UNIT,
+              "e2e_ms": ref_e2e_ms, "e2e_value": evals / (ref_e2e_ms * 1e-3),
+              "what": "the reference's own kernels.cu (built for sm_100a) through its StackSearch on this GPU: "
+                      "psi/phi preloaded (ms_per_search, best of 2) and uploaded inside the call (e2e_ms)"}
+    return parity, timing
+
+
 def run_ours(args, c, cfg_name):
     from kbmod_b200 import search as kb
     from kbmod_b200 import dist
@@ -268,10 +345,22 @@ def run_ours(args, c, cfg_name):
         rows = c["H"] // c["band_div"]
         mid = rank * c["H"] + c["H"] // 2
         band = (mid - rows // 2, mid - rows // 2 + rows)
+    use_band = band if (world > 1 or c.get("band_div")) else None
+
+    # ---- one-shot pipeline, as KBMOD drives the API (run_search.py:363-378): construct, search once, read results --
+    # Timed on the host clock from the first byte of the host images to the result list on the host; the device is
+    # idle before and after.  `e2e_first_search` is the search + read part of the same pass.
     t0 = time.perf_counter()
     s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"])
     ctor_s = time.perf_counter() - t0
-    configure(s, c, band if (world > 1 or c.get("band_div")) else None)
+    configure(s, c, use_band)
+    t1 = time.perf_counter()
+    s.search_all((vx, vy), True)
+    first = s.get_results_array()
+    t2 = time.perf_counter()
+    first_tm = s.last_timing()
+    first_ms, with_ctor_ms = 1e3 * (t2 - t1), 1e3 * (t2 - t0)
+    first_digest = results_digest(first)
     evals_rank = c["W"] * (band[1] - band[0] if strong else rows) * len(vx) * c["T"]
     evals_job = c["W"] * c["H"] * len(vx) * c["T"] if strong else evals_rank * world
     stack_bytes = s.psi_phi_array.total_array_size
@@ -305,6 +394,7 @@ def run_ours(args, c, cfg_name):
         ms_dev = comm.max_float(ms_dev)
         k_ms = comm.max_float(k_ms)
     n_results = s.get_number_total_results()
+    resident_digest = results_digest(s.get_results_array())
     ms_step = ms_dev / args.steps
     value = evals_job / (ms_step * 1e-3)
 
@@ -330,46 +420,46 @@ def run_ours(args, c, cfg_name):
     ms_e2e = max(ms_e2e_dev, wall_e2e) / e2e_steps  # results are read after the last kernel: use the wall clock
     if comm is not None:
         ms_e2e = comm.max_float(ms_e2e)
+        first_ms = comm.max_float(first_ms)
+        with_ctor_ms = comm.max_float(with_ctor_ms)
     e2e_value = evals_job / (ms_e2e * 1e-3)
 
-    # ---- roofline of the dominant kernel (the search kernel), from CUDA events inside the library ----------------
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
-    else:
-        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-    bytes_per_eval = {-1: 8, 4: 8, 2: 4, 1: 2}[c["nb"]]
+    # ---- roofline of the dominant kernel (the gather kernel), CUDA events inside the library around that launch -----
+    # The gathers are served from shared memory (the stack is staged by TMA), so the binding roof is the SM's
+    # shared-memory pipe; its peak for this encoding's load width, the L2-resident gather figure and the HBM
+    # streaming figure are measured here, in this process, by kb_measure_peaks.
+    pk = measure_peaks()
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_copy = float(json.load(open(peaks_file))["hbm_gbs"]) if os.path.exists(peaks_file) else 6650.0
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if os.path.exists(peaks_file) else "fallback (B200_PROFILING.md)"
+    nbytes = {-1: 4, 4: 4, 2: 2, 1: 1}[c["nb"]]
+    bytes_per_eval = 2 * nbytes
+    smem_key = {4: "smem_lds64", 2: "smem_lds32", 1: "smem_lds16"}[nbytes]
     kernel_ms = k_ms / max(n_kernel, 1)
     achieved = evals_rank * bytes_per_eval / (kernel_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get((cfg_name, bool(tiled))), "traffic_unit": "bytes/launch",
-                "kernel": "search_tiled_kernel" if tiled else "search_generic_kernel",
-                "kernel_ms": kernel_ms, "bytes_per_eval": bytes_per_eval, "peak_source": peak_src,
-                "note": "algorithmic gather bytes (P*N*T pairs) / kernel time; gathers are served from shared "
-                        "memory / L2, so the fraction of the HBM copy peak can exceed 1"}
-
-    # The gathers never go to HBM: the stack is staged once into shared memory by TMA, so the binding resource is the
-    # shared-memory pipe.  Measured on this pool by scripts/peaks_micro.cu (profiles/r01_peaks_micro.jsonl):
-    # L2-resident 256 B row gather and LDS.64 bandwidth -- the "L2 gather roofline" the metric names and the
-    # roofline of the resource the kernel actually runs on.
-    micro = os.path.join(ROOT, "profiles", "r01_peaks_micro.jsonl")
-    if os.path.exists(micro):
-        pk = {}
-        for ln in open(micro):
-            ln = ln.strip()
-            if ln.startswith("{"):
-                d = json.loads(ln)
-                pk[d["what"]] = d["GBps"]
-        if "l2_resident_row_gather_256B" in pk:
-            roofline["l2_gather"] = {"peak": pk["l2_resident_row_gather_256B"], "unit": "GB/s",
-                                     "frac": achieved / pk["l2_resident_row_gather_256B"],
-                                     "peak_source": "scripts/peaks_micro.cu, L2-resident 256 B row gather, measured"}
-        if "smem_lds64" in pk and tiled:
-            roofline["shared_memory"] = {"peak": pk["smem_lds64"], "unit": "GB/s", "frac": achieved / pk["smem_lds64"],
-                                         "peak_source": "scripts/peaks_micro.cu, LDS.64 on all SMs, measured",
-                                         "note": "algorithmic gather bytes / time against the LDS.64 peak; pairs "
-                                                 "shared by neighbouring candidates are read once, so this too "
-                                                 "can exceed the bytes actually moved"}
+    traffic_tab = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    ncu = json.load(open(traffic_tab)).get(cfg_name) if os.path.exists(traffic_tab) else None
+    kname = "search_tiled_kernel" if tiled else "search_generic_kernel"
+    if ncu is not None and kname not in ncu["kernel"]:
+        ncu = None
+    bound_peak = pk[smem_key] if tiled else pk["l2_row_gather_256B"]
+    roofline = {"bound": "shared_memory" if tiled else "l2", "achieved": achieved, "peak": bound_peak, "unit": "GB/s",
+                "frac": achieved / bound_peak,
+                "traffic": ncu["dram_bytes"] if ncu else None, "traffic_unit": "bytes/launch (dram read + write)",
+                "traffic_source": ncu["source"] if ncu else None,
+                "kernel": kname, "kernel_ms": kernel_ms, "bytes_per_eval": bytes_per_eval,
+                "peak_source": f"kb_measure_peaks in this run: {smem_key} (shared-memory loads of this encoding's "
+                               f"pair width on all SMs)" if tiled else "kb_measure_peaks in this run: L2-resident 256 B row gather",
+                "peaks_measured_in_run_gbs": pk, "hbm_copy_peak_gbs": hbm_copy, "hbm_copy_peak_source": hbm_src,
+                "note": "achieved = algorithmic gather bytes (P*N*T pairs x bytes per pair) / gather-kernel time"}
+    flat = {"kernel_ms": kernel_ms, "achieved_gbs": achieved,
+            "frac_shared_memory": achieved / pk[smem_key], "peak_shared_memory": pk[smem_key],
+            "frac_l2_gather": achieved / pk["l2_row_gather_256B"], "peak_l2_gather": pk["l2_row_gather_256B"],
+            "frac_hbm": achieved / hbm_copy, "peak_hbm": hbm_copy,
+            "wavefronts_per_gather": (ncu["smem_wavefronts"] / (evals_rank / 32.0)) if ncu else None,
+            "e2e_first_search_ms": first_ms, "e2e_first_search": evals_job / (first_ms * 1e-3),
+            "e2e_with_ctor_ms": with_ctor_ms, "e2e_with_ctor": evals_job / (with_ctor_ms * 1e-3),
+            "ctor_seconds": ctor_s}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
@@ -382,8 +472,27 @@ def run_ours(args, c, cfg_name):
                        if world > 1 else "single GPU", "results": int(n_results), "ctor_seconds": ctor_s},
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d + 8 * len(vx)),
-                    "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e, "steps": e2e_steps},
+                    "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e, "steps": e2e_steps,
+                    "first_search_h2d_bytes": int(first_tm["h2d_stack_bytes"])},
             "gpu_launches": int(launches), "clocks": clocks}
+    line.update(flat)
+    # every leg returned the same list (one-shot, resident, and -- below -- the reference's)
+    line["legs_identical"] = bool(first_digest == resident_digest) if comm is None else None
+
+    if comm is not None:
+        # NCCL-merged list of all ranks against one GPU searching the whole frame alone (rank 0, outside the timing)
+        merged = results_digest(s.get_results_array())
+        if rank == 0:
+            ymin, ymax = (0, c["H"]) if strong else (0, c["H"] * world)
+            if c.get("band_div") and not strong:
+                line["merge_check"] = "skipped (bands of a band_div config do not tile the frame)"
+            else:
+                s.set_start_bounds_y(ymin, ymax)
+                s.search_all((vx, vy), True)
+                whole = results_digest(s.get_results_array())
+                line["merge_check"] = "identical" if whole == merged else "differs"
+                line["merge_check_n"] = int(s.get_number_total_results())
+        comm.barrier()
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -393,8 +502,17 @@ def run_ours(args, c, cfg_name):
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": evals / dt, "unit": UNIT, "cores": cores, "kind": "reference",
                                     "sample": sample, "seconds": dt}
+            del ss
         except Exception as e:  # the reference build did not travel: fall back to the C port of the oracle
             line["cpu_baseline"] = cpu_baseline_port(c, stack, vx, vy, str(e))
+    if rank == 0 and world == 1 and not args.no_parity and c["T"] <= 200 and not c.get("band_div"):
+        try:
+            del s
+            line["parity"], line["reference_gpu"] = reference_gpu_leg(c, stack, vx, vy)
+            line["vs_reference_gpu"] = value / line["reference_gpu"]["value"]
+            line["vs_reference_gpu_e2e"] = e2e_value / line["reference_gpu"]["e2e_value"]
+        except Exception as e:
+            line["parity"] = {"vs": "reference_gpu", "unavailable": str(e)[:200]}
     if comm is not None:
         comm.finalize()
     if rank == 0:
@@ -426,6 +544,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the reference-GPU parity / timing leg")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every GPU searches its own copy-sized band of an N-times taller frame (default, "
                          "the driver's scaling run); strong = the named frame, start-pixel rows split over the GPUs "

@@ -199,6 +199,12 @@ KB_EXPORT int kb_extract_stamps(const float *const *sci, int T, int H, int W, co
  * elapsed milliseconds between the two. */
 KB_EXPORT int kb_timer_start(kb_handle h);
 KB_EXPORT int kb_timer_stop(kb_handle h, float *ms);
+/* Roofline denominators measured on the current device, in this process (no reference counterpart; SURVEY.md 8d
+ * asks for a measured L2 figure beside the HBM one).  gbps[0..5] receive, in GB/s: HBM streaming read, L2-resident
+ * streaming read, L2-resident 256-byte row gather, and the shared-memory bandwidth of 64-, 32- and 16-bit loads
+ * per lane (the access shapes of the float32, uint16 and uint8 gathers of the tiled search kernel).  Takes about
+ * 0.2 s and 2 GB of device memory for its duration.  n = capacity of gbps (at least 6). */
+KB_EXPORT int kb_measure_peaks(double *gbps, int n);
 
 /* ---- for callers that cannot allocate device memory --------------------------------------------------------
  * No counterpart in the reference (its sort is a host-side __gnu_parallel::sort, trajectory_list.cpp:96-107).

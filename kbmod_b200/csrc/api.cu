@@ -67,6 +67,9 @@ struct kb_stack_s {
     void *host_array = nullptr;  // reference layout [t][row][col][psi,phi]
     bool host_pinned = false;
     void *d_search = nullptr;  // canonical pitched search copy
+    uint32_t *d_screen = nullptr;  // 16-bit fixed-point screening copy of the same pixels (StackView::screen)
+    float q_step_psi = 1.0f, q_step_phi = 1.0f;  // its quantisation steps; known once the stack's value range is
+    bool q_known = false;
     double *d_times = nullptr;
     bool on_gpu = false;
     int zero_marker = 0;  // form of the search copy (StackView::zero_marker)
@@ -107,6 +110,9 @@ static StackView make_view(kb_handle h) {
     sv.phi_min = h->meta.phi_min_val;
     sv.phi_scale = h->meta.phi_scale;
     sv.zero_marker = h->zero_marker;
+    sv.screen = h->d_screen;
+    sv.q_step_psi = h->q_step_psi;
+    sv.q_step_phi = h->q_step_phi;
     return sv;
 }
 
@@ -233,8 +239,10 @@ static kb_handle new_handle() {
 static void free_device_stack(kb_handle h, bool keep_alloc = false) {
     if (!keep_alloc) {
         if (h->d_search) cudaFree(h->d_search);
+        if (h->d_screen) cudaFree(h->d_screen);
         if (h->d_times) cudaFree(h->d_times);
         h->d_search = nullptr;
+        h->d_screen = nullptr;
         h->d_times = nullptr;
     }
     h->on_gpu = false;
@@ -264,29 +272,67 @@ static void destroy_handle(kb_handle h) {
     delete h;
 }
 
+// Quantisation steps of the screening copy from the largest |psi| and |phi| of the stack: 32767 steps reach it.
+static void set_screen_steps(kb_handle h, float amax_psi, float amax_phi) {
+    auto step = [](float a) {
+        if (!(a > 0.0f) || !std::isfinite(a)) return 1.0f;
+        const float s = a / 32767.0f;
+        return (s > 0.0f && std::isfinite(1.0f / s)) ? s : 1.0f;   // denormal range: screening is useless but safe
+    };
+    h->q_step_psi = step(amax_psi);
+    h->q_step_phi = step(amax_phi);
+    h->q_known = true;
+}
+
 // PsiPhiArray::move_to_gpu (psi_phi_array.cpp:74-111): upload + canonicalise into the pitched search copy.
 static void upload_stack(kb_handle h) {
     if (h->on_gpu) return;
     const size_t pb = pair_bytes(h->nb);
     const size_t rows = (size_t)h->T * h->H;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
     KB_CUDA(cudaMemcpy2DAsync(h->d_search, (size_t)h->Wp * pb, h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, rows,
                               cudaMemcpyHostToDevice, h->stream));
     h->zero_marker = 0;
     const char *nozm = getenv("KB_NO_ZERO_MARKER");
-    if (h->nb == 4 && !(nozm && nozm[0] == '1')) {
+    if (h->nb == 4 && h->zm_known < 0) {
+        // One look at a float stack the first time it comes up (the host copy never changes afterwards): may
+        // invalid pairs be stored as (0, 0)?
         DevBuf<uint32_t> d_flag;
         d_flag.ensure(1);
         launch_detect_valid_zero_pairs(h->d_search, h->Wp, h->T, h->H, h->W, d_flag.p, h->stream);
         uint32_t flag = 1;
         KB_CUDA(cudaMemcpyAsync(&flag, d_flag.p, sizeof(flag), cudaMemcpyDeviceToHost, h->stream));
         KB_CUDA(cudaStreamSynchronize(h->stream));
-        h->zero_marker = flag ? 0 : 1;
+        h->zm_known = (flag || (nozm && nozm[0] == '1')) ? 0 : 1;
     }
-    h->zm_known = h->zero_marker;
+    if (h->nb != 4) h->zm_known = 0;
+    h->zero_marker = h->zm_known;
     launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, h->stream);
+    if (!h->q_known) {
+        // ... and how large do the values get: the quantisation steps of the screening copy
+        if (h->nb == 4) {
+            DevBuf<uint32_t> d_mm;
+            d_mm.ensure(4);
+            launch_minmax_pitched(h->d_search, rows * h->Wp, d_mm.p, h->stream);  // canonical: padding is invalid
+            uint32_t out[4];
+            KB_CUDA(cudaMemcpyAsync(out, d_mm.p, sizeof(out), cudaMemcpyDeviceToHost, h->stream));
+            KB_CUDA(cudaStreamSynchronize(h->stream));
+            float amax[2] = {0.0f, 0.0f};
+            for (int k = 0; k < 2; ++k)
+                if (out[2 * k] <= out[2 * k + 1])
+                    amax[k] = std::max(fabsf(ordered_to_float(out[2 * k])), fabsf(ordered_to_float(out[2 * k + 1])));
+            set_screen_steps(h, amax[0], amax[1]);
+        } else {
+            set_screen_steps(h, std::max(fabsf(h->meta.psi_min_val), fabsf(h->meta.psi_max_val)),
+                             std::max(fabsf(h->meta.phi_min_val), fabsf(h->meta.phi_max_val)));
+        }
+    }
+    launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
+                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, 0,
+                         h->H, h->stream);
     h->on_gpu = true;
 }
 
@@ -297,7 +343,7 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     if (getenv("KB_DEBUG"))
         fprintf(stderr, "[kbmod_b200] pipelined upload? on_gpu=%d zm_known=%d pinned=%d\n", (int)h->on_gpu, h->zm_known,
                 (int)h->host_pinned);
-    if (h->on_gpu || h->zm_known < 0 || !h->host_pinned) return false;
+    if (h->on_gpu || h->zm_known < 0 || !h->q_known || !h->host_pinned) return false;
     const char *off = getenv("KB_NO_PIPELINED_UPLOAD");
     if (off && off[0] == '1') return false;
     const size_t pb = pair_bytes(h->nb);
@@ -318,6 +364,7 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     }
     const int64_t span = row_hi - row_lo;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     UploadProgress &up = h->up;
     if (!h->copy_stream) {
@@ -334,8 +381,11 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     KB_CUDA(cudaStreamWaitEvent(h->copy_stream, up.ready, 0));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->copy_stream));
     if (const char *poison = getenv("KB_POISON_STACK"))  // tests: rows that are not uploaded must never be read
-        if (poison[0] == '1') KB_CUDA(cudaMemsetAsync(h->d_search, 0xA5, rows * h->Wp * pb, h->copy_stream));
-    h->zero_marker = h->zm_known;
+        if (poison[0] == '1') {
+            KB_CUDA(cudaMemsetAsync(h->d_search, 0xA5, rows * h->Wp * pb, h->copy_stream));
+            KB_CUDA(cudaMemsetAsync(h->d_screen, 0xA5, rows * h->Wp * sizeof(uint32_t), h->copy_stream));
+        }
+    h->zero_marker = (h->nb == 4) ? h->zm_known : 0;
     up.n_chunks = UploadProgress::kMaxChunks;
     for (int c = 0; c < up.n_chunks; ++c) {
         const int r0 = row_lo + (int)(span * c / up.n_chunks), r1 = row_lo + (int)(span * (c + 1) / up.n_chunks);
@@ -350,6 +400,9 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
         KB_CUDA(cudaMemcpy3DAsync(&q, h->copy_stream));
         launch_canonicalise_rows(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0,
                                  r1 - r0, h->copy_stream);
+        launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
+                             h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi,
+                             r0, r1 - r0, h->copy_stream);
         up.row_end[c] = r1;
         KB_CUDA(cudaEventRecord(up.ev[c], h->copy_stream));
     }
@@ -669,7 +722,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
         }
         if (!pipelined) upload_stack(h);
         h->timing.h2d_stack_bytes = copied;
-        launches += pipelined ? UploadProgress::kMaxChunks : (h->nb == 4 ? 2 : 1);  // canonicalise (+ zero detection) kernels
+        launches += pipelined ? 2 * UploadProgress::kMaxChunks : 2;  // canonicalise + quantise kernels
     }
     t_h2d.stop(st);
 

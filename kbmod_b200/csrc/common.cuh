@@ -58,6 +58,10 @@ struct StackView {
     // float sum is an exact no-op, so the search kernel can accumulate without testing validity.  Chosen at upload
     // time when no *valid* pair is (0, 0) (upload_stack checks), which keeps "pair is zero" == "pair is invalid".
     int zero_marker;
+    // Screening copy [t][row][Wp] of 32-bit words (psi_phi.cu quantise_kernel): psi and phi as signed 16-bit
+    // multiples of q_step_psi / q_step_phi, invalid pair = 0.  Only the tiled kernel's gather loop reads it.
+    const uint32_t *screen;
+    float q_step_psi, q_step_phi;
 };
 
 // Per-pixel result slot written by the search kernels: 16 bytes, [pixel][K].
@@ -145,6 +149,12 @@ int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, in
                         int zero_marker, cudaStream_t st);
 int launch_canonicalise_rows(const void *d_src, int src_pitch, void *d_dst, int T, int H, int W, int Wp, int nb,
                              int zero_marker, int r0, int nr, cudaStream_t st);
+// The screening copy (one 32-bit word per pair: two signed 16-bit fixed-point numbers, 0 = invalid) of rows
+// [r0, r0 + nr) of every image, from the canonical search copy; and the min/max reduction over a float search copy.
+int launch_quantise_rows(const void *d_search, uint32_t *d_screen, int T, int H, int Wp, int nb, int zero_marker,
+                         float psi_scale, float psi_min, float phi_scale, float phi_min, float step_psi,
+                         float step_phi, int r0, int nr, cudaStream_t st);
+int launch_minmax_pitched(const void *d_search, uint64_t n_pairs, uint32_t *d_mm, cudaStream_t st);
 // float stacks: sets *d_flag to 1 when some valid pair is exactly (0, 0) (then the zero marker cannot be used).
 int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int H, int W, uint32_t *d_flag,
                                    cudaStream_t st);

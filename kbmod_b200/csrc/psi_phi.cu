@@ -345,4 +345,76 @@ int launch_canonicalise(const void *d_src, int src_pitch, void *d_dst, int T, in
     return launch_canonicalise_rows(d_src, src_pitch, d_dst, T, H, W, Wp, nb, zero_marker, 0, H, st);
 }
 
+// ---- the screening copy: every pair of the canonical search copy as two signed 16-bit fixed-point numbers ----------
+// word = (uint16)rint(psi / step_psi) | (uint16)rint(phi / step_phi) << 16, an invalid pair = 0.  The search kernel
+// adds these words up exactly, in integers, to bound a candidate's likelihood from above; candidates that cannot be
+// ruled out are then evaluated exactly from the search copy.  |value - q * step| <= 0.502 * step (the quotient's own
+// rounding included); a valid pair whose two numbers both round to 0 gets phi = 1 instead (one more half step), so
+// that "word == 0" means "no data" -- which is what the kernel's error bound (search_tiled.cu, screen_bounds) and
+// its observation counter assume.
+__device__ __forceinline__ int quantise_value(float v, float step) {
+    const int q = __float2int_rn(__fdiv_rn(v, step));
+    return max(-32767, min(32767, q));
+}
+
+template <int NB>
+__global__ void quantise_kernel(const void *__restrict__ src, uint32_t *__restrict__ dst, int T, int H, int r0, int nr,
+                                int Wp, int zero_marker, float psi_scale, float psi_min, float phi_scale,
+                                float phi_min, float step_psi, float step_phi) {
+    const uint64_t total = (uint64_t)T * nr * (uint64_t)Wp;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t g = stack_row(i / Wp, H, r0, nr) * (uint64_t)Wp + i % Wp;
+        float a, b;
+        bool ok;
+        if (NB == 4) {
+            const float2 v = reinterpret_cast<const float2 *>(src)[g];
+            a = v.x;
+            b = v.y;
+            ok = zero_marker ? (((__float_as_uint(a) | __float_as_uint(b)) << 1) != 0u) : (b == b);
+        } else if (NB == 2) {
+            const ushort2 v = reinterpret_cast<const ushort2 *>(src)[g];
+            ok = v.x != 0;  // canonical: both or none
+            a = ok ? (float)__dadd_rn(__dmul_rn((double)v.x - 1.0, (double)psi_scale), (double)psi_min) : 0.0f;
+            b = ok ? (float)__dadd_rn(__dmul_rn((double)v.y - 1.0, (double)phi_scale), (double)phi_min) : 0.0f;
+        } else {
+            const uchar2 v = reinterpret_cast<const uchar2 *>(src)[g];
+            ok = v.x != 0;
+            a = ok ? (float)__dadd_rn(__dmul_rn((double)v.x - 1.0, (double)psi_scale), (double)psi_min) : 0.0f;
+            b = ok ? (float)__dadd_rn(__dmul_rn((double)v.y - 1.0, (double)phi_scale), (double)phi_min) : 0.0f;
+        }
+        uint32_t w = 0u;
+        if (ok) {
+            const int qa = quantise_value(a, step_psi);
+            int qb = quantise_value(b, step_phi);
+            if (qa == 0 && qb == 0) qb = 1;
+            w = ((uint32_t)qa & 0xffffu) | ((uint32_t)qb << 16);
+        }
+        dst[g] = w;
+    }
+}
+
+int launch_quantise_rows(const void *d_search, uint32_t *d_screen, int T, int H, int Wp, int nb, int zero_marker,
+                         float psi_scale, float psi_min, float phi_scale, float phi_min, float step_psi,
+                         float step_phi, int r0, int nr, cudaStream_t st) {
+    if (nr <= 0) return 0;
+    if (nb == 4)
+        quantise_kernel<4><<<148 * 8, 256, 0, st>>>(d_search, d_screen, T, H, r0, nr, Wp, zero_marker, psi_scale, psi_min,
+                                                    phi_scale, phi_min, step_psi, step_phi);
+    else if (nb == 2)
+        quantise_kernel<2><<<148 * 8, 256, 0, st>>>(d_search, d_screen, T, H, r0, nr, Wp, zero_marker, psi_scale, psi_min,
+                                                    phi_scale, phi_min, step_psi, step_phi);
+    else
+        quantise_kernel<1><<<148 * 8, 256, 0, st>>>(d_search, d_screen, T, H, r0, nr, Wp, zero_marker, psi_scale, psi_min,
+                                                    phi_scale, phi_min, step_psi, step_phi);
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
+// max |psi| and max |phi| over the valid pairs of a canonical float search copy (padding and invalid pairs are NaN
+// or zero and do not matter): d_mm = {psi_min, psi_max, phi_min, phi_max} as ordered uints, like launch_minmax.
+int launch_minmax_pitched(const void *d_search, uint64_t n_pairs, uint32_t *d_mm, cudaStream_t st) {
+    return launch_minmax(reinterpret_cast<const float2 *>(d_search), n_pairs, d_mm, st);
+}
+
 }  // namespace kb

@@ -158,10 +158,14 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 // The reference's exchange sort leaves equal lc values in a history-dependent order; that order only matters
 // when two tied observations carry different (psi, phi).  In that (rare) case *needs_serial is set and the
 // caller falls back to sigmag_recompute for bit-exactness.  Result is warp-uniform.  T <= 32*E.
+// What comes back is exactly what evaluateTrajectory leaves in the trajectory (kernels.cu:154-242): the unclipped
+// lh / flux (sums in time order; -1 when phi_sum <= 0) if there are too few observations or that lh is below min_lh
+// (kernels.cu:201-203: the clip is skipped), the clipped values otherwise.
 template <int NB, int E>
 __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
-                                            float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float &lh,
-                                            float &flux, int &n_valid, bool &needs_serial, float2 *ws = nullptr) {
+                                            float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float min_lh,
+                                            float &lh, float &flux, int &n_valid, bool &needs_serial,
+                                            float2 *ws = nullptr) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     float a[E], b[E], lc[E];
@@ -184,8 +188,23 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     }
     needs_serial = false;
     n_valid = n;
-    // kernels.cu:201-203: too few observations (or none) -> the clip is skipped; the caller decides what that means
-    if (n < min_obs || n == 0) return;
+    {   // kernels.cu:175-197: the unclipped sums, valid observations in time order (every lane runs the same chain)
+        float ups = 0.0f, uph = 0.0f;
+#pragma unroll
+        for (int es = 0; es < E; ++es) {
+            const int nsrc = min(32, sv.T - es * 32);  // warp-uniform
+            for (int ls = 0; ls < nsrc; ++ls) {
+                const float va = __shfl_sync(FULL, a[es], ls), vb = __shfl_sync(FULL, b[es], ls);
+                if ((okm[es] >> ls) & 1u) {
+                    ups = __fadd_rn(ups, va);
+                    uph = __fadd_rn(uph, vb);
+                }
+            }
+        }
+        finish_sums(ups, uph, lh, flux);
+    }
+    // kernels.cu:201-203: too few observations (or none), or an unclipped lh below min_lh -> the clip is skipped
+    if (n < min_obs || n == 0 || lh < min_lh) return;
     // rank[e] = position of my element in ascending order (ties: earlier image first).
     // Fast pass: count the strictly smaller and the equal values (invalid observations travel as NaN, which
     // compares false both ways).  Without equal values -- the usual case -- the count of smaller ones is the rank.
@@ -322,25 +341,23 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     finish_sums(ps, ph, lh, flux);
 }
 
-// Handles every lane of the warp that `need`s the sigma-G recomputation, one lane at a time, cooperatively.
-// (x, y, vx, vy) are the caller's per-lane values.  For the lanes that needed it: n_valid receives the number of
-// valid observations; lh/flux are replaced by the clipped values when n_valid >= max(min_obs, 1) (otherwise the
-// reference skips the clip, kernels.cu:201-203, and lh/flux are left as they were).
+template <int NB, bool SIGMAG, int MAXT>
+__device__ __forceinline__ void evaluate_exact(const StackView &sv, const double *times, const kb_params &p, int x,
+                                               int y, float vx, float vy, float &lh, float &flux, int &obs,
+                                               uint8_t *mask);
+
+// Evaluates, for every lane of the warp that `need`s it, the whole of evaluateTrajectory with sigma-G on
+// (kernels.cu:154-242), one lane at a time, cooperatively.  (x, y, vx, vy) are the caller's per-lane values.  For
+// the lanes that needed it: n_valid receives the number of valid observations; lh/flux receive the unclipped values
+// when the reference skips the clip (n_valid < min_obs, n_valid == 0 or unclipped lh < min_lh; kernels.cu:201-203),
+// the clipped ones otherwise.
 // MAXT <= 256 selects the cooperative routine (E = MAXT/32); larger stacks use the serial routine.
 template <int NB, int MAXT>
 __device__ __noinline__ void sigmag_for_lanes(bool need, const StackView &sv, const double *times, int x, int y,
                                                  float vx, float vy, const kb_params &p, float &lh, float &flux,
                                                  int &n_valid, float2 *ws = nullptr) {
     if constexpr (MAXT > 256) {
-        if (need) {
-            float l2 = lh, f2 = flux;
-            sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, l2, f2, nullptr,
-                                       &n_valid);
-            if (!(n_valid < p.min_observations || n_valid == 0)) {
-                lh = l2;
-                flux = f2;
-            }
-        }
+        if (need) evaluate_exact<NB, true, MAXT>(sv, times, p, x, y, vx, vy, lh, flux, n_valid, nullptr);
         return;
     } else {
     constexpr int E = (MAXT + 31) / 32;
@@ -354,17 +371,15 @@ __device__ __noinline__ void sigmag_for_lanes(bool need, const StackView &sv, co
         float rl = 0.0f, rf = 0.0f;
         int rn = 0;
         bool serial;
-        warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, p.min_observations, rl, rf,
-                           rn, serial, ws);
+        warp_sigmag<NB, E>(sv, times, bx, by, bvx, bvy, p.sgl_L, p.sgl_H, p.sigmag_coeff, p.min_observations, p.min_lh,
+                           rl, rf, rn, serial, ws);
         if (lane == L) {
             n_valid = rn;
-            if (serial)
+            lh = rl;
+            flux = rf;
+            if (serial)   // tied lc values with different payloads: the reference's exchange-sort order decides
                 sigmag_recompute<NB, MAXT>(sv, times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
                                            nullptr);
-            else if (!(rn < p.min_observations || rn == 0)) {
-                lh = rl;
-                flux = rf;
-            }
         }
     }
     }

@@ -1,4 +1,6 @@
-// search_tiled.cu -- the throughput path of the search: a TMA-staged, time-tiled gather-reduce kernel.
+// search_tiled.cu -- the throughput path of the search: a TMA-staged, time-tiled gather-reduce kernel that screens
+// every (start pixel, candidate) with exact integer sums over a 16-bit fixed-point copy of the stack and evaluates
+// exactly only what the screening cannot rule out (see search_tiled_kernel.cuh).
 //
 // Decomposition (B200-first, not the reference's one-thread-per-pixel serial loop):
 //   * A CTA owns a tile of 32 x BY start pixels (one consumer warp per row, lanes along x) and visits the
@@ -75,14 +77,14 @@ static inline bool tab_offset(float v, double t, int &off) {
     return r == 0.0 && (q - 0.5) == prod;                   // exactly on a boundary: no rounding anywhere
 }
 
-static bool decode_is_exact_in_fp32(int nb, float scale, float mn) {
-    const unsigned n = (nb == 1) ? 255u : 65535u;
-    for (unsigned code = 1; code <= n; ++code) {
-        const float ref = (float)(((double)(float)code - 1.0) * (double)scale + (double)mn);
-        const float fast = fmaf((float)(code - 1), scale, mn);
-        if (memcmp(&ref, &fast, 4) != 0) return false;
-    }
-    return true;
+// Bounds of |reference float sum - step * exact integer sum| over T observations (see the kernel's header):
+//   quantisation: <= 0.502 step per observation for psi; phi may be moved by one more half step so that a valid pair
+//                 never maps to the word 0 (1.002 step); 0.52 / 1.02 leave room for the kernel's own float products
+//   the reference's sequential float sum: <= T^2 * 2^-24 * max|value| = T^2 * step / 512 (max|value| <= 32767.5 step)
+static void screen_bounds(int T, float step_psi, float step_phi, float &e_psi, float &e_phi) {
+    const double t = (double)T;
+    e_psi = (float)((double)step_psi * (0.52 * t + t * t / 500.0 + 2.0));
+    e_phi = (float)((double)step_phi * (1.02 * t + t * t / 500.0 + 2.0));
 }
 
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
@@ -96,11 +98,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     if (n_cand == 0) return no("no candidates");
     if (p.do_sigmag_filter && T > kMaxTSigma) return no("too many images for sigma-G");
     if (sizeof(double) * (size_t)T > 16 * 1024) return no("too many images for the tiled kernel's time table");
-    if (sv.nb != 4) {
-        if (!decode_is_exact_in_fp32(sv.nb, sv.psi_scale, sv.psi_min) ||
-            !decode_is_exact_in_fp32(sv.nb, sv.phi_scale, sv.phi_min))
-            return no("fp32 decode would not be bit-exact for this scale/offset");
-    }
+    if (!sv.screen) return no("no screening copy of the stack");
+    if ((double)T * 32767.0 >= 2147483647.0) return no("too many images for 32-bit screening sums");
     std::vector<double> times(T);
     if (h_times) {
         std::copy(h_times, h_times + T, times.begin());
@@ -113,8 +112,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
         if (!std::isfinite(t)) return no("non-finite time");
         tabs = std::max(tabs, fabs(t));
     }
-    const int PB = 2 * sv.nb;
-    const int bw_limit = (sv.nb == 4) ? 128 : 256;  // TMA box: at most 256 elements along x
+    const int PB = kScreenPairBytes;  // the TMA boxes come from the screening copy: one 32-bit word per pixel
+    const int bw_limit = 256;         // TMA box: at most 256 elements along x
 
     // ---- candidates whose offsets cannot be tabulated exactly go to the exact list ---------------------------------
     const int N = (int)n_cand;
@@ -134,7 +133,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     // A group's box is (TBX + sx) x (TBY + sy) pixels with sx, sy ~ velocity extent * max|t|; each cut goes
     // across the direction that shrinks that box most, at a multiple of TG so the leaves come out full.
     const int XA = 16 / PB;                          // TMA: box origin must be 16-byte aligned in global memory
-    const int bw_round = (sv.nb == 1) ? 16 : 8;      // keeps every TMA destination 128-byte aligned
+    const int bw_round = 8;                          // keeps every TMA destination 128-byte aligned
     const int sy_lim = 40;
     const int rows_lim = (TBY + sy_lim + TCH - 1) / TCH * TCH;
     const int w_cap = std::min(TBX + bw_round + (NMAPS - 1) * bw_round, bw_limit);  // widest tensor-map box
@@ -315,6 +314,15 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     v.clipq = nullptr;
     v.clip_cnt = nullptr;
     v.clip_cap = 0;
+    v.step_psi = sv.q_step_psi;
+    v.step_phi = sv.q_step_phi;
+    screen_bounds(T, sv.q_step_psi, sv.q_step_phi, v.e_psi, v.e_phi);
+    {
+        const float bar = p.min_lh, b2 = bar * bar * 0.99999f;
+        v.bar_ok = (p.do_sigmag_filter && bar > 0.0f && bar < 1.0e15f) ? 1 : 0;
+        v.bar_c3 = v.bar_ok ? v.step_phi * b2 : 0.0f;
+        v.bar_c4 = v.bar_ok ? -v.e_phi * b2 : 0.0f;
+    }
     plan->smem = (size_t)TS * (STAGE_BYTES + HDR_BYTES) + 2 * TS * 8 + sizeof(double) * (size_t)T;
     // Rows a tile can touch below its origin: the deepest box bottom of any group; candidates evaluated per pixel
     // (exact list, winners in the epilogue, clips) go as far as their own last offset.
@@ -324,21 +332,18 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     plan->reach_hi = reach_hi;
     v.pixel_base = 0;
 
-    // ---- tensor maps over the search copy: dims (x elements, rows, images), one per box width ------------------
-    const bool f32 = sv.nb == 4;
-    const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
-                                       : (sv.nb == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16);
-    const cuuint64_t gdim[3] = {(cuuint64_t)(f32 ? 2 * sv.W : sv.W), (cuuint64_t)sv.H, (cuuint64_t)sv.T};
+    // ---- tensor maps over the screening copy: dims (pixels, rows, images) of 32-bit words, one per box width; what
+    // lies outside the image is filled with zeros by the TMA unit == the screening copy's "no data" word
+    const cuuint64_t gdim[3] = {(cuuint64_t)sv.W, (cuuint64_t)sv.H, (cuuint64_t)sv.T};
     const cuuint64_t gstr[2] = {(cuuint64_t)sv.Wp * PB, (cuuint64_t)sv.Wp * PB * sv.H};
     const cuuint32_t estr[3] = {1, 1, 1};
     for (int i = 0; i < NMAPS; ++i) {
         const int bw = std::min(w_base + i * w_step, w_max);
-        const cuuint32_t box[3] = {(cuuint32_t)(f32 ? 2 * bw : bw), (cuuint32_t)TCH, 1};
-        const CUresult r = encode_fn()(&plan->maps.m[i], dt, 3, const_cast<void *>(sv.data), gdim, gstr, box, estr,
+        const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)TCH, 1};
+        const CUresult r = encode_fn()(&plan->maps.m[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3,
+                                       const_cast<uint32_t *>(sv.screen), gdim, gstr, box, estr,
                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                       (f32 && !sv.zero_marker) ? CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA
-                                                                : CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
             cudaFree(plan->d_block);
             plan->d_block = nullptr;

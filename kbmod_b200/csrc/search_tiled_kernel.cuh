@@ -11,15 +11,35 @@
 
 namespace kb {
 
-static constexpr int TBX = 32;         // tile width  (lanes)
-static constexpr int TBY = 15;         // tile height (consumer warps); +1 producer warp = 512 threads
+#ifndef KB_TBY
+#define KB_TBY 15
+#endif
+#ifndef KB_TCH
+#define KB_TCH 8
+#endif
+#ifndef KB_TPX
+#define KB_TPX 2
+#endif
+#ifndef KB_TG
+#define KB_TG 8
+#endif
+static constexpr int TPX = KB_TPX;     // start pixels per lane along x: x, x + 32, ...
+static constexpr int TBX = 32 * TPX;   // tile width
+static constexpr int TBY = KB_TBY;     // tile height (consumer warps); +1 producer warp
 static constexpr int TNT = (TBY + 1) * 32;
-static constexpr int TG = 16;          // candidates per group
-static constexpr int TS = 4;           // pipeline stages
-static constexpr int TCH = 4;          // rows per TMA box
+static constexpr int TG = KB_TG;       // candidates per group
+#ifndef KB_TS
+#define KB_TS 4
+#endif
+#ifndef KB_STAGE_KB
+#define KB_STAGE_KB 48
+#endif
+static constexpr int TS = KB_TS;       // pipeline stages
+static constexpr int TCH = KB_TCH;     // rows per TMA box
 static constexpr int TMAXTC = 8;       // max images per stage
-static constexpr int STAGE_BYTES = 48 * 1024;
+static constexpr int STAGE_BYTES = KB_STAGE_KB * 1024;
 static constexpr int NMAPS = 16;       // tensor maps with box widths base, base+step, ...
+static constexpr int kScreenPairBytes = 4;  // one 32-bit word of the screening copy per pixel pair
 
 // One pipeline stage as the host lays it out (and as it lands in shared memory by one bulk copy):
 //   meta   {nt | last << 8, group, t0, tx_bytes}
@@ -47,6 +67,12 @@ struct PlanView {
     unsigned long long *clip_cnt;  // [0] requests, [1] survivors, [2] clipped in line (queue full)
     unsigned long long clip_cap;
     unsigned pixel_base;            // start-pixel index of this launch's first pixel within the whole search area
+    // screening: value of one quantisation step and the bound of |reference float sum - step * integer sum|
+    float step_psi, step_phi, e_psi, e_phi;
+    // sigma-G searches: the bar is min_lh for every pixel; bar_c3 = step_phi * bar^2, bar_c4 = -e_phi * bar^2 (both
+    // scaled by 0.99999), bar_ok = 0 when min_lh is not a positive squarable number (then nothing is screened out)
+    float bar_c3, bar_c4;
+    int bar_ok;
 };
 
 struct TiledPlan {
@@ -73,15 +99,17 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
                  "r"(bytes)
                  : "memory");
 }
+// The wait suspends the warp in hardware for up to the hinted time before it reports "not yet" (a spinning warp
+// takes issue slots from the warps that have work).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
             "{\n\t.reg .pred p;\n\t"
             "WAIT_LOOP:\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
             "@p bra DONE;\n\t"
             "bra WAIT_LOOP;\n\t"
             "DONE:\n\t}" ::"r"(bar),
-            "r"(parity)
+            "r"(parity), "r"(20000u)
             : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2,
@@ -97,58 +125,30 @@ __device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_
                  : "memory");
 }
 
-// ---- pair decode from shared memory ---------------------------------------------------------------------
-template <int NB>
-struct PairLoad;
-template <>
-struct PairLoad<4> {
-    static constexpr int kPairBytes = 8;
-    template <bool ZM>
-    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
-        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(psi), "=f"(phi) : "r"(addr));
-        // canonical copy: an invalid pair is (+0, +0) in zero-marker form, else (NaN, NaN)
-        if (ZM) return ((__float_as_uint(psi) | __float_as_uint(phi)) << 1) != 0u;
-        return phi == phi;
-    }
-};
-// Encoded stacks: the host verified (plan creation) that fmaf((float)(code-1), scale, min) reproduces the
-// reference's fp64 decode for every code, so the gather decodes in fp32.
-template <>
-struct PairLoad<2> {
-    static constexpr int kPairBytes = 4;
-    template <bool ZM>
-    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
-        uint32_t w;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
-        const float a = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)) - 8388609.0f;  // code - 1, exact
-        const float b = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)) - 8388609.0f;
-        psi = fmaf(a, sv.psi_scale, sv.psi_min);
-        phi = fmaf(b, sv.phi_scale, sv.phi_min);
-        return w != 0u;  // canonical copy: an invalid pair is (0, 0)
-    }
-};
-template <>
-struct PairLoad<1> {
-    static constexpr int kPairBytes = 2;
-    template <bool ZM>
-    __device__ static __forceinline__ bool load(uint32_t addr, const StackView &sv, float &psi, float &phi) {
-        uint16_t h;
-        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(addr));
-        const uint32_t w = h;
-        const float a = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440)) - 8388609.0f;
-        const float b = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7441)) - 8388609.0f;
-        psi = fmaf(a, sv.psi_scale, sv.psi_min);
-        phi = fmaf(b, sv.phi_scale, sv.phi_min);
-        return w != 0u;
-    }
-};
+template <int OFF>
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t w;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(w) : "r"(addr), "n"(OFF));
+    return w;
+}
 
 // ---- the kernel -----------------------------------------------------------------------------------------
-// ZM (float stacks in zero-marker form, StackView::zero_marker): invalid pairs and out-of-image pixels read as
-// (+0, +0), so the inner loop adds unconditionally.
-// COUNT: keep a per-candidate observation count in registers.  Only needed when sigma-G is off and min_obs > 0;
-// with sigma-G on, the count of the few candidates that reach min_lh falls out of the clip's own re-gather.
-template <int NB, bool ZM, bool COUNT, bool SIGMAG, int MAXT, int K>
+// The gather loop works on the SCREENING copy of the stack (StackView::screen): one 32-bit word per pixel pair, psi
+// and phi as signed 16-bit multiples of sv.q_step_psi / sv.q_step_phi, 0 for an invalid pair (and for everything
+// outside the image: the TMA unit fills with zeros).  Per (start pixel, candidate, image) it costs one LDS.32 and
+// two IDP.2A (dp2a picks one 16-bit half and adds it to a 32-bit sum), and the sums are EXACT integers, so
+//     | psi_sum_ref - step_psi * P |  <=  pv.e_psi,      | phi_sum_ref - step_phi * F |  <=  pv.e_phi
+// hold rigorously for the reference's float sums (quantisation <= 0.502 / 1.002 steps per observation, float
+// summation error <= T^2 * 2^-24 * max|value|; screen_bounds() in search_tiled.cu).  From them an upper bound of the
+// candidate's likelihood follows; a candidate whose bound is below the bar (min_lh with sigma-G on, else the pixel's
+// current K-th best) cannot appear in the results and is dropped.  Everything else -- a tiny fraction -- is
+// evaluated EXACTLY from the search copy with the reference's own arithmetic: through the deferred clip queue when
+// sigma-G is on (clip_kernel re-gathers, checks the unclipped likelihood, clips), in line otherwise.  The result is
+// therefore identical to evaluating every candidate exactly; the screening only decides how much work that takes.
+// NB is the encoding of the exact search copy (4 = float, 2 = uint16, 1 = uint8), used by the exact routines only.
+// COUNT: keep a per-candidate observation count (sigma-G off and min_obs > 0), so candidates with too few
+// observations are dropped before the exact evaluation.
+template <int NB, bool COUNT, bool SIGMAG, int MAXT, int K>
 __global__ void __launch_bounds__(TNT, 1)
         search_tiled_kernel(const __grid_constant__ TmapSet maps, const PlanView pv, const StackView sv,
                             const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
@@ -174,8 +174,7 @@ __global__ void __launch_bounds__(TNT, 1)
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
     const int n_stages = pv.n_stages;
-    constexpr int PB = PairLoad<NB>::kPairBytes;
-    constexpr int XE = (NB == 4) ? 2 : 1;  // tensor-map elements per pixel along x
+    constexpr int PB = kScreenPairBytes;
 
     if (warp == TBY) {
         // ===================== producer warp: TMA box loads + the stage record =================================
@@ -207,7 +206,7 @@ __global__ void __launch_bounds__(TNT, 1)
                 const int nrows = bxz & 0xffff, widx = bxz >> 16;
                 if (i < total && ch * TCH < nrows) {
                     const int pitch = pv.w_base + pv.w_step * widx;
-                    tma_load_3d(stage_base + bxw + ch * TCH * pitch * PB, &maps.m[widx], XE * (tile_x0 + bxx),
+                    tma_load_3d(stage_base + bxw + ch * TCH * pitch * PB, &maps.m[widx], tile_x0 + bxx,
                                 tile_y0 + bxy + ch * TCH, t0 + k, full);
                 }
             }
@@ -216,18 +215,30 @@ __global__ void __launch_bounds__(TNT, 1)
         }
     } else {
         // ===================== consumer warps: gather, reduce, rank ========================================
-        const int px = tile_x0 + lane, py = tile_y0 + warp;
-        const bool in_bounds = (px - p.x_start_min) < sw && (py - p.y_start_min) < sh;
-        const unsigned pixel_index = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px - p.x_start_min));
-        float psi[TG], phi[TG];
-        int cnt[COUNT ? TG : 1];
-        TopK<K> top;
-        top.init();
+        // A lane owns TPX start pixels of its row: x, x + 32, ...  Their words for one (candidate, image) lie 128
+        // bytes apart in the staged box, so one address serves all of them (immediate offsets).
+        const int py = tile_y0 + warp;
+        int px[TPX];
+        bool in_bounds[TPX];
+        unsigned pixel_index[TPX];
 #pragma unroll
-        for (int j = 0; j < TG; ++j) {
-            psi[j] = 0.0f;
-            phi[j] = 0.0f;
-            if (COUNT) cnt[j] = 0;
+        for (int h = 0; h < TPX; ++h) {
+            px[h] = tile_x0 + lane + 32 * h;
+            in_bounds[h] = (px[h] - p.x_start_min) < sw && (py - p.y_start_min) < sh;
+            pixel_index[h] = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px[h] - p.x_start_min));
+        }
+        int P[TPX][TG], F[TPX][TG];
+        int cnt[COUNT ? TPX : 1][COUNT ? TG : 1];
+        TopK<K> top[TPX];
+#pragma unroll
+        for (int h = 0; h < TPX; ++h) {
+            top[h].init();
+#pragma unroll
+            for (int j = 0; j < TG; ++j) {
+                P[h][j] = 0;
+                F[h][j] = 0;
+                if (COUNT) cnt[h][j] = 0;
+            }
         }
         for (int s = 0; s < n_stages; ++s) {
             const int slot = s % TS;
@@ -242,43 +253,22 @@ __global__ void __launch_bounds__(TNT, 1)
                 const int pitch = pv.w_base + pv.w_step * (bx.z >> 16);
                 const uint32_t bk = base + bx.w + (uint32_t)((warp * pitch + lane) * PB);
                 const int4 *ofs = reinterpret_cast<const int4 *>(hdr->offs[k]);
-                // Neighbouring candidates of a group often land on the same pixel of an image (always for t ~ 0,
-                // mostly for dense velocity grids); the host orders a group as a chain of nearest neighbours, and
-                // inside each run of four a candidate whose offset equals its predecessor's reuses the pair already
-                // in registers.  The comparison is warp-uniform (offsets are per (candidate, image), not per pixel);
-                // the four runs stay independent so their loads overlap.  Only where it compiles to predicated
-                // loads (float pairs, no observation counter); the other variants load every time.
-                constexpr bool DEDUP = (NB == 4) && !COUNT;
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
                     const int4 o = ofs[j4];
                     const int off[4] = {o.x, o.y, o.z, o.w};
-                    float a = 0.0f, b = 0.0f;
-                    bool ok = false;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int j = j4 * 4 + q;
-                        if (!DEDUP || q == 0 || off[q] != off[q - 1])
-                            ok = PairLoad<NB>::template load<ZM>(bk + off[q], sv, a, b);
-                        if (ZM) {
-                            psi[j] = __fadd_rn(psi[j], a);
-                            phi[j] = __fadd_rn(phi[j], b);
-                            if (COUNT && NB == 4) {
-                                // valid <=> the pair is not (+-0, +-0): one LOP3 with a predicate result and one
-                                // predicated add in place (the compiler's select form costs two more per gather)
-                                asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
-                                    "lop3.b32 t, %1, 0x7fffffff, %2, 0xc8;\n\t"
-                                    "setp.ne.u32 p, t, 0;\n\t"
-                                    "@p add.s32 %0, %0, 1;\n\t}"
-                                    : "+r"(cnt[j])
-                                    : "r"(__float_as_uint(a)), "r"(__float_as_uint(b)));
-                            } else if (COUNT && ok) {
-                                cnt[j] += 1;
-                            }
-                        } else if (ok) {
-                            psi[j] = __fadd_rn(psi[j], a);
-                            phi[j] = __fadd_rn(phi[j], b);
-                            if (COUNT) cnt[j] += 1;
+                        const uint32_t addr = bk + off[q];
+                        uint32_t w[TPX];
+                        w[0] = lds_u32<0>(addr);
+                        if (TPX > 1) w[TPX - 1] = lds_u32<32 * PB>(addr);
+#pragma unroll
+                        for (int h = 0; h < TPX; ++h) {
+                            P[h][j] = __dp2a_lo((int)w[h], 0x0001, P[h][j]);   // += low half  (psi, signed 16 bit)
+                            F[h][j] = __dp2a_lo((int)w[h], 0x0100, F[h][j]);   // += high half (phi)
+                            if (COUNT) cnt[h][j] += (w[h] != 0u) ? 1 : 0;  // the quantiser never maps a valid pair to 0
                         }
                     }
                 }
@@ -286,59 +276,101 @@ __global__ void __launch_bounds__(TNT, 1)
             __syncwarp();
             if (lane == 0) mbar_arrive(empty);
             if (meta.x >> 8) {
-                // ---- all images of this group are in: turn sums into ranked candidates -------------------
+                // ---- all images of this group are in: which candidates can still matter? ------------------
+                // The reference's lh = psi_sum / sqrt(phi_sum) can reach the bar (> 0) only if
+                //     psi_hi > 0  and  psi_hi^2 >= bar^2 * phi_lo,    psi_hi = step_psi P + e_psi,
+                //                                                    phi_lo = step_phi F - e_phi
+                // (phi_lo <= 0 puts no bound on the quotient; the right-hand side is then <= 0 and only the sign
+                // of psi_hi decides -- with psi_sum <= 0 the lh is <= 0 or, for phi_sum <= 0, -1, below any bar
+                // > 0).  The 1e-5 taken off bar^2 covers the roundings of this test and of the reference's own
+                // division and square root.  A bar that is not a positive, squarable number: no screening.
                 const int g = meta.y;
+                unsigned passmask = 0u;   // bit h * TG + j: candidate j of the group needs the exact evaluation
 #pragma unroll
-                for (int j = 0; j < TG; ++j) {
-                    const int c = __ldg(pv.cand + g * TG + j);  // warp-uniform
-                    const float ps = psi[j], ph = phi[j];
-                    psi[j] = 0.0f;
-                    phi[j] = 0.0f;
-                    int seen = 0;
-                    if (COUNT) {
-                        seen = cnt[j];
-                        cnt[j] = 0;
-                    }
-                    if (c < 0) continue;
-                    bool alive = !COUNT || seen >= p.min_observations;  // kernels.cu:318 obs_count < min_obs
-                    // Conservative reject: est approximates lh to ~1e-6 relative; anything clearly below the
-                    // bar (min_lh when sigma-G is on, else the current K-th best) cannot matter.
-                    const float bar_lh = SIGMAG ? p.min_lh : top.worst();
-                    const float est = (ph > 0.0f) ? ps * rsqrtf(ph) : -1.0f;
-                    alive = alive && !(est < bar_lh - (fabsf(est) + fabsf(bar_lh)) * 2e-6f - 1e-30f);
-                    if (!SIGMAG) {
-                        if (!alive) continue;
-                        float lh, flux;
-                        finish_sums(ps, ph, lh, flux);
-                        if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
+                for (int h = 0; h < TPX; ++h) {
+                    float c3, c4;
+                    bool screen;
+                    if (SIGMAG) {
+                        c3 = pv.bar_c3;
+                        c4 = pv.bar_c4;
+                        screen = pv.bar_ok != 0;
                     } else {
-                        if (!__any_sync(0xffffffffu, alive)) continue;
-                        float lh = -1.0f, flux = -1.0f;
-                        if (alive) finish_sums(ps, ph, lh, flux);
-                        alive = alive && !(lh < p.min_lh);  // kernels.cu:201-203 then :319
-                        // The clip itself is deferred: append (pixel, candidate) to the global queue; clip_kernel
-                        // works it off afterwards with every SM (the requests cluster around bright sources).
-                        alive = alive && in_bounds;
-                        const unsigned am = __ballot_sync(0xffffffffu, alive);
-                        if (am) {
-                            unsigned long long base_slot = 0;
-                            if (lane == 0) base_slot = atomicAdd(pv.clip_cnt, (unsigned long long)__popc(am));
-                            base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
-                            const unsigned long long slot_q = base_slot + __popc(am & ((1u << lane) - 1u));
-                            bool inline_need = false;
-                            if (alive) {
-                                if (slot_q < pv.clip_cap) pv.clipq[slot_q] = make_uint2(pixel_index, (unsigned)c);
-                                else inline_need = true;
+                        const float bar = top[h].worst();
+                        screen = bar > 0.0f && bar < 1.0e15f;
+                        const float b2 = bar * bar * 0.99999f;
+                        c3 = pv.step_phi * b2;
+                        c4 = -pv.e_phi * b2;
+                    }
+#pragma unroll
+                    for (int j = 0; j < TG; ++j) {
+                        const float t = fmaf(__int2float_rn(P[h][j]), pv.step_psi, pv.e_psi);
+                        const float r = fmaf(__int2float_rn(F[h][j]), c3, c4);
+                        P[h][j] = 0;
+                        F[h][j] = 0;
+                        bool alive = in_bounds[h] && (!screen || (t > 0.0f && t * t >= r));
+                        if (COUNT) {
+                            alive = alive && cnt[h][j] >= p.min_observations;   // kernels.cu:318 obs_count < min_obs
+                            cnt[h][j] = 0;
+                        }
+                        passmask |= alive ? (1u << (h * TG + j)) : 0u;
+                    }
+                }
+                unsigned wm = passmask;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) wm |= __shfl_xor_sync(0xffffffffu, wm, d);
+                while (wm) {   // warp-uniform loop over the (pixel slot, candidate) pairs some lane still needs
+                    const int b = __ffs(wm) - 1;
+                    wm &= wm - 1;
+                    const int h = b / TG, j = b % TG;
+                    const int c = __ldg(pv.cand + g * TG + j);
+                    if (c < 0) continue;   // padding of an incomplete group
+                    const bool alive = (passmask >> b) & 1u;
+                    const int x = (h == 0) ? px[0] : px[TPX - 1];
+                    static_assert(TPX <= 2, "pixel selection below handles two pixels per lane");
+                    if (!SIGMAG) {
+                        if (alive) {
+                            float lh, flux;
+                            int obs;
+                            evaluate_exact<NB, false, 1>(sv, s_times, p, x, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux,
+                                                         obs, nullptr);
+                            if (!(obs < p.min_observations)) {
+                                if (h == 0) {
+                                    if (beats(lh, c, top[0].worst(), top[0].cand[K - 1])) top[0].insert(lh, c);
+                                } else {
+                                    if (beats(lh, c, top[TPX - 1].worst(), top[TPX - 1].cand[K - 1]))
+                                        top[TPX - 1].insert(lh, c);
+                                }
                             }
-                            if (__any_sync(0xffffffffu, inline_need)) {  // queue full: clip it here and now
-                                int nv = 0;
-                                sigmag_for_lanes<NB, MAXT>(inline_need, sv, s_times, px, py, __ldg(cvx + c),
-                                                           __ldg(cvy + c), p, lh, flux, nv);
-                                if (inline_need) {
-                                    atomicAdd(pv.clip_cnt + 2, 1ull);
-                                    if (!(nv < p.min_observations) && !(lh < p.min_lh) &&
-                                        beats(lh, c, top.worst(), top.cand[K - 1]))
-                                        top.insert(lh, c);
+                        }
+                    } else {
+                        // The exact evaluation (unclipped lh against min_lh, then the clip) is deferred: append
+                        // (pixel, candidate) to the global queue; clip_kernel works it off afterwards with every SM
+                        // (the requests cluster around bright sources).
+                        const unsigned am = __ballot_sync(0xffffffffu, alive);
+                        unsigned long long base_slot = 0;
+                        if (lane == 0) base_slot = atomicAdd(pv.clip_cnt, (unsigned long long)__popc(am));
+                        base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+                        const unsigned long long slot_q = base_slot + __popc(am & ((1u << lane) - 1u));
+                        bool inline_need = false;
+                        if (alive) {
+                            const unsigned pi = (h == 0) ? pixel_index[0] : pixel_index[TPX - 1];
+                            if (slot_q < pv.clip_cap) pv.clipq[slot_q] = make_uint2(pi, (unsigned)c);
+                            else inline_need = true;
+                        }
+                        if (__any_sync(0xffffffffu, inline_need)) {  // queue full: evaluate it here and now
+                            int nv = 0;
+                            float lh = -1.0f, flux = -1.0f;
+                            sigmag_for_lanes<NB, MAXT>(inline_need, sv, s_times, x, py, __ldg(cvx + c), __ldg(cvy + c), p,
+                                                       lh, flux, nv);
+                            if (inline_need) {
+                                atomicAdd(pv.clip_cnt + 2, 1ull);
+                                if (!(nv < p.min_observations) && !(lh < p.min_lh)) {
+                                    if (h == 0) {
+                                        if (beats(lh, c, top[0].worst(), top[0].cand[K - 1])) top[0].insert(lh, c);
+                                    } else {
+                                        if (beats(lh, c, top[TPX - 1].worst(), top[TPX - 1].cand[K - 1]))
+                                            top[TPX - 1].insert(lh, c);
+                                    }
                                 }
                             }
                         }
@@ -346,34 +378,37 @@ __global__ void __launch_bounds__(TNT, 1)
                 }
             }
         }
-        // ---- candidates whose offsets could not be tabulated exactly: full per-pixel arithmetic ----------
-        for (int e = 0; e < pv.n_exact; ++e) {
-            const int c = __ldg(pv.exact + e);
-            float lh, flux;
-            int obs;
-            evaluate_exact<NB, SIGMAG, MAXT>(sv, s_times, p, px, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux, obs,
-                                             nullptr);
-            if (obs < p.min_observations || (SIGMAG && lh < p.min_lh)) continue;
-            if (beats(lh, c, top.worst(), top.cand[K - 1])) top.insert(lh, c);
-        }
-        // ---- epilogue: flux and obs_count of the winners, written in the reference's slot order ------------
-        const int xi = px - p.x_start_min, yi = py - p.y_start_min;
 #pragma unroll
-        for (int r = 0; r < K; ++r) {
-            if (r >= (int)p.results_per_pixel) break;  // warp-uniform
-            Slot out{-FLT_MAX, 0.0f, 0, -1};
-            const int c = top.cand[r];
-            const float vx = (c >= 0) ? __ldg(cvx + c) : 0.0f, vy = (c >= 0) ? __ldg(cvy + c) : 0.0f;
-            float lh = 0.0f, flux = 0.0f;
-            int obs = 0;
-            if (c >= 0) evaluate_exact<NB, false, 1>(sv, s_times, p, px, py, vx, vy, lh, flux, obs, nullptr);
-            if (SIGMAG) {
-                const bool need = c >= 0 && !(obs < p.min_observations || obs == 0 || lh < p.min_lh);
-                int nv = obs;
-                sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px, py, vx, vy, p, lh, flux, nv);
+        for (int h = 0; h < TPX; ++h) {
+            // ---- candidates whose offsets could not be tabulated exactly: full per-pixel arithmetic ----------
+            for (int e = 0; e < pv.n_exact; ++e) {
+                const int c = __ldg(pv.exact + e);
+                float lh, flux;
+                int obs;
+                evaluate_exact<NB, SIGMAG, MAXT>(sv, s_times, p, px[h], py, __ldg(cvx + c), __ldg(cvy + c), lh, flux, obs,
+                                                 nullptr);
+                if (obs < p.min_observations || (SIGMAG && lh < p.min_lh)) continue;
+                if (beats(lh, c, top[h].worst(), top[h].cand[K - 1])) top[h].insert(lh, c);
             }
-            if (c >= 0) out = Slot{lh, flux, obs, c};
-            if (xi < sw && yi < sh) slots[((size_t)yi * sw + xi) * p.results_per_pixel + r] = out;
+            // ---- epilogue: flux and obs_count of the winners, written in the reference's slot order ------------
+            const int xi = px[h] - p.x_start_min, yi = py - p.y_start_min;
+#pragma unroll
+            for (int r = 0; r < K; ++r) {
+                if (r >= (int)p.results_per_pixel) break;  // warp-uniform
+                Slot out{-FLT_MAX, 0.0f, 0, -1};
+                const int c = top[h].cand[r];
+                const float vx = (c >= 0) ? __ldg(cvx + c) : 0.0f, vy = (c >= 0) ? __ldg(cvy + c) : 0.0f;
+                float lh = 0.0f, flux = 0.0f;
+                int obs = 0;
+                if (c >= 0) evaluate_exact<NB, false, 1>(sv, s_times, p, px[h], py, vx, vy, lh, flux, obs, nullptr);
+                if (SIGMAG) {
+                    const bool need = c >= 0 && !(obs < p.min_observations || obs == 0 || lh < p.min_lh);
+                    int nv = obs;
+                    sigmag_for_lanes<NB, MAXT>(need, sv, s_times, px[h], py, vx, vy, p, lh, flux, nv);
+                }
+                if (c >= 0) out = Slot{lh, flux, obs, c};
+                if (xi < sw && yi < sh) slots[((size_t)yi * sw + xi) * p.results_per_pixel + r] = out;
+            }
         }
     }
 }
@@ -405,8 +440,10 @@ __global__ void __launch_bounds__(256)
         int nv = 0;
         sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, __ldg(cvx + c), __ldg(cvy + c), p, lh, flux, nv, ws);
         if (lane == 0) {
-            // Queued candidates had an unclipped lh >= min_lh.  The clip replaces lh/flux when it ran
-            // (nv >= max(min_obs, 1)); nv < min_obs is rejected (kernels.cu:318); nv == 0 keeps lh = flux = -1.
+            // Queued candidates only passed the screening bound.  sigmag_for_lanes returns what evaluateTrajectory
+            // does (kernels.cu:154-242): the unclipped lh when it is below min_lh or there are too few
+            // observations (lh = flux = -1 when there is none), else the clipped one; kernels.cu:318-320 then
+            // rejects nv < min_obs and lh < min_lh.
             if (!(nv < p.min_observations) && !(lh < p.min_lh)) {
                 const unsigned long long k = atomicAdd(cnt + 1, 1ull);  // counts past surv_cap too: host reruns
                 if (k < surv_cap) surv[k] = ClipSurvivor{it.x, c, lh, flux, nv};
@@ -432,12 +469,12 @@ static void launch_clip(const StackView &sv, const kb_params &p, const float *d_
     KB_CUDA(cudaGetLastError());
 }
 
-template <int NB, bool ZM, bool COUNT, bool SIGMAG, int MAXT>
+template <int NB, bool COUNT, bool SIGMAG, int MAXT>
 static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                      Slot *d_slots, dim3 grid, cudaStream_t st) {
 #define KB_LAUNCH_T(KK)                                                                                         \
     do {                                                                                                        \
-        auto kfn = search_tiled_kernel<NB, ZM, COUNT, SIGMAG, MAXT, KK>;                                                   \
+        auto kfn = search_tiled_kernel<NB, COUNT, SIGMAG, MAXT, KK>;                                            \
         KB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan->smem));       \
         kfn<<<grid, TNT, plan->smem, st>>>(plan->maps, plan->v, sv, p, d_vx, d_vy, d_slots);                    \
     } while (0)
@@ -446,17 +483,17 @@ static void launch_k(TiledPlan *plan, const StackView &sv, const kb_params &p, c
 #undef KB_LAUNCH_T
 }
 
-template <int NB, bool ZM>
+template <int NB>
 static void launch_nb(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
     if (!plan->sigmag) {
-        if (p.min_observations > 0) launch_k<NB, ZM, true, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-        else launch_k<NB, ZM, false, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    } else if (sv.T <= 32) launch_k<NB, ZM, false, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else if (sv.T <= 64) launch_k<NB, ZM, false, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    // (a MAXT = 256 instantiation makes ptxas spill the accumulators of the gather loop; the serial sigma-G routine
-    // of the large variant only runs for the K winners of a pixel and when the clip queue overflows)
-    else launch_k<NB, ZM, false, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+        if (p.min_observations > 0) launch_k<NB, true, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+        else launch_k<NB, false, false, 1>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    } else if (sv.T <= 32) launch_k<NB, false, true, 32>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    else if (sv.T <= 64) launch_k<NB, false, true, 64>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    // (the serial sigma-G routine of the large variant only runs for the K winners of a pixel and when the clip
+    // queue overflows)
+    else launch_k<NB, false, true, kMaxTSigma>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
 // One entry per stack encoding (defined in search_tiled_nb*.cu).

@@ -5,7 +5,7 @@ namespace kb {
 
 void launch_tiled_nb2(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
-    launch_nb<2, false>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    launch_nb<2>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
 void launch_clip_nb2(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,

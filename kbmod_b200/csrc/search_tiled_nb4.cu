@@ -5,8 +5,7 @@ namespace kb {
 
 void launch_tiled_nb4(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                       Slot *d_slots, dim3 grid, cudaStream_t st) {
-    if (sv.zero_marker) launch_nb<4, true>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
-    else launch_nb<4, false>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
+    launch_nb<4>(plan, sv, p, d_vx, d_vy, d_slots, grid, st);
 }
 
 void launch_clip_nb4(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,

@@ -1,0 +1,86 @@
+// Pipe-rate probe for the integer screening loop: how many warp-instructions per clock per SM the device sustains for
+//   (0) dp2a (IDP.2A)   (1) 32-bit integer add (IADD3)   (2) FADD   (3) the loop shape LDS.32 + IADD + 2 x dp2a
+//   (4) the float loop shape LDS.64 + IADD + 2 x FADD
+// Build + run on the box:  nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o /tmp/idp scripts/idp_micro.cu && /tmp/idp
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+template <int MODE>
+__global__ void __launch_bounds__(512, 1) probe(int iters, const int *offs_g, int *out) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ int offs[64];
+    for (int i = threadIdx.x; i < 96 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t *>(sm)[i] = i * 2654435761u;
+    if (threadIdx.x < 64) offs[threadIdx.x] = offs_g[threadIdx.x];
+    __syncthreads();
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm) + (threadIdx.x & 31) * (MODE == 4 ? 8 : 4) + (threadIdx.x >> 5) * 1024;
+    int a[16], b[16];
+    float fa[16], fb[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { a[j] = j; b[j] = -j; fa[j] = j; fb[j] = -j; }
+    for (int k = 0; k < iters; ++k) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (MODE == 0) {
+                a[j] = __dp2a_lo(a[j] ^ k, 0x0001, b[j]);
+                b[j] = __dp2a_lo(b[j], 0x0100, a[j]);
+            } else if (MODE == 1) {
+                a[j] = a[j] + (b[j] ^ k);
+                b[j] = b[j] + (a[j] ^ k);
+            } else if (MODE == 2) {
+                fa[j] = fa[j] + fb[j];
+                fb[j] = fb[j] + 1.0f;
+            } else if (MODE == 3) {
+                uint32_t w;
+                const uint32_t addr = sbase + offs[(j + k) & 63];
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
+                a[j] = __dp2a_lo((int)w, 0x0001, a[j]);
+                b[j] = __dp2a_lo((int)w, 0x0100, b[j]);
+            } else {
+                float x, y;
+                const uint32_t addr = sbase + offs[(j + k) & 63];
+                asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x), "=f"(y) : "r"(addr));
+                fa[j] += x;
+                fb[j] += y;
+            }
+        }
+    }
+    int s = 0;
+    float fs = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { s += a[j] + b[j]; fs += fa[j] + fb[j]; }
+    if (s == 0x12345678 || fs == 123.456f) out[0] = s;
+}
+
+template <int MODE>
+static void run(const char *name, int per_iter_instr, const int *d_offs, int *d_out, int sms, double clk_hz) {
+    cudaFuncSetAttribute(probe<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    const int iters = 4000;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    probe<MODE><<<sms, 512, 96 * 1024>>>(iters, d_offs, d_out); cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; ++r) {
+        cudaEventRecord(e0); probe<MODE><<<sms, 512, 96 * 1024>>>(iters, d_offs, d_out); cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
+    }
+    const double warp_instr = (double)sms * 16 * iters * 16.0 * per_iter_instr;   // 16 warps x 16 bodies
+    const double clks = best * 1e-3 * clk_hz;
+    printf("{\"what\": \"%s\", \"ms\": %.3f, \"warp_bodies_per_clk_per_sm\": %.3f, \"counted_instr_per_clk_per_sm\": %.3f, \"err\": \"%s\"}\n", name, best,
+           (double)16 * iters * 16.0 / clks, warp_instr / sms / clks, cudaGetErrorString(cudaGetLastError()));
+}
+
+int main() {
+    cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
+    int clk_khz = 0; cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0);
+    int h_offs[64]; for (int i = 0; i < 64; ++i) h_offs[i] = ((i * 37) % 61) * 128 * 4 % 60000;
+    for (int i = 0; i < 64; ++i) h_offs[i] &= ~7;
+    int *d_offs, *d_out; cudaMalloc(&d_offs, sizeof(h_offs)); cudaMalloc(&d_out, 4);
+    cudaMemcpy(d_offs, h_offs, sizeof(h_offs), cudaMemcpyHostToDevice);
+    const int sms = prop.multiProcessorCount; const double hz = clk_khz * 1e3;
+    run<0>("dp2a x2", 2, d_offs, d_out, sms, hz);
+    run<1>("iadd x2 (+xor)", 2, d_offs, d_out, sms, hz);
+    run<2>("fadd x2", 2, d_offs, d_out, sms, hz);
+    run<3>("lds32 + iadd + 2 dp2a", 4, d_offs, d_out, sms, hz);
+    run<4>("lds64 + iadd + 2 fadd", 4, d_offs, d_out, sms, hz);
+    return 0;
+}

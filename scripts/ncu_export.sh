@@ -29,6 +29,24 @@ def val(r):
     except Exception: return 0.0
 if col is not None:
     body.sort(key=val, reverse=True)
+# instruction mix over ALL SASS lines: executed warp-instructions and stall samples per opcode
+import collections
+icol = next((j for j, c in enumerate(h) if c.strip() == "Instructions Executed"), None)
+scol = next((j for j, c in enumerate(h) if c.strip() == "Source"), 1)
+mix, smp = collections.Counter(), collections.Counter()
+def num(x):
+    try: return float(x)
+    except Exception: return 0.0
+for r in body:
+    t = r[scol].split()
+    op = (t[1] if t and t[0].startswith("@") and len(t) > 1 else (t[0] if t else "?")).rstrip(";")
+    if icol is not None: mix[op] += num(r[icol])
+    if col is not None: smp[op] += num(r[col])
+ti, ts = sum(mix.values()) or 1.0, sum(smp.values()) or 1.0
+with open(f"gpurun_out/{tag}_opcode_mix.txt", "w") as f:
+    f.write(f"# executed warp-instructions {ti:.4e}, stall samples {ts:.0f}\n")
+    for op, v in mix.most_common(60):
+        f.write(f"{op:32s} {v:14.4e} {100 * v / ti:6.2f}%   samples {100 * smp[op] / ts:6.2f}%\n")
 w = csv.writer(open(f"gpurun_out/{tag}_source_top.csv", "w"))
 w.writerow(h)
 for r in body[:400]:
