@@ -259,8 +259,10 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             if (nt == 0) t0 = t;
             cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 16), used);
             group_reach[g] = std::max(group_reach[g], mny + rows_pad);
+            cur.img[nt].slot_off = used;
+            cur.img[nt].pitch_bytes = pitch * PB;
             for (int j = 0; j < TG; ++j)
-                cur.offs[nt][j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
+                cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
             used += bytes;
             tx += bytes;
             ++nt;

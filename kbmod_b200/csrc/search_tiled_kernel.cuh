@@ -43,15 +43,20 @@ static constexpr int kScreenPairBytes = 4;  // one 32-bit word of the screening 
 
 // One pipeline stage as the host lays it out (and as it lands in shared memory by one bulk copy):
 //   meta   {nt | last << 8, group, t0, tx_bytes}
-//   box[k] {ox, oy, nrows | widx << 16, slot_off}   for the nt images of the stage (k < TMAXTC)
-//   offs[k][j] byte offset of candidate j's pixel inside image k's slot, relative to the thread's own pixel
+//   box[k] {ox, oy, nrows | widx << 16, slot_off}   for the nt images of the stage (k < TMAXTC): the producer's view
+//   img[k] what a consumer needs for image k: where its box starts in the stage, the box's row pitch in bytes, and
+//          offs[j], the byte offset of candidate j's pixel inside the box relative to the thread's own pixel
+struct ImageRec {
+    int slot_off, pitch_bytes, pad[2];
+    int offs[TG];
+};
 struct StageRec {
     int4 meta;
     int4 box[TMAXTC];
-    int pad[4];
-    int offs[TMAXTC][TG];
+    ImageRec img[TMAXTC];
 };
-static_assert(sizeof(StageRec) % 16 == 0 && offsetof(StageRec, offs) % 16 == 0, "bulk copies need 16-byte units");
+static_assert(sizeof(StageRec) % 16 == 0 && offsetof(StageRec, img) % 16 == 0 && sizeof(ImageRec) % 16 == 0,
+              "bulk copies and 128-bit shared loads need 16-byte units");
 static constexpr int HDR_BYTES = (sizeof(StageRec) + 127) / 128 * 128;
 
 struct TmapSet {
@@ -125,6 +130,18 @@ __device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_
                  : "memory");
 }
 
+template <int OFF>
+__device__ __forceinline__ int4 lds_v4(uint32_t addr) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4+%5];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr), "n"(OFF));
+    return v;
+}
+template <int OFF>
+__device__ __forceinline__ int2 lds_v2(uint32_t addr) {
+    int2 v;
+    asm volatile("ld.shared.v2.s32 {%0, %1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(addr), "n"(OFF));
+    return v;
+}
 template <int OFF>
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     uint32_t w;
@@ -227,6 +244,7 @@ __global__ void __launch_bounds__(TNT, 1)
             in_bounds[h] = (px[h] - p.x_start_min) < sw && (py - p.y_start_min) < sh;
             pixel_index[h] = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px[h] - p.x_start_min));
         }
+        const uint32_t hdr0 = smem_u32(s_hdr), stage0 = smem_u32(s_stage);
         int P[TPX][TG], F[TPX][TG];
         int cnt[COUNT ? TPX : 1][COUNT ? TG : 1];
         TopK<K> top[TPX];
@@ -244,18 +262,18 @@ __global__ void __launch_bounds__(TNT, 1)
             const int slot = s % TS;
             const uint32_t full = bar0 + 8 * slot, empty = bar0 + 8 * (TS + slot);
             mbar_wait(full, (s / TS) & 1);
-            const StageRec *hdr = reinterpret_cast<const StageRec *>(s_hdr + (size_t)slot * HDR_BYTES);
-            const int4 meta = hdr->meta;
+            const uint32_t hdr_a = hdr0 + (uint32_t)slot * HDR_BYTES;
+            const int4 meta = lds_v4<0>(hdr_a);
             const int nt = meta.x & 0xff;
-            const uint32_t base = smem_u32(s_stage + (size_t)slot * STAGE_BYTES);
-            for (int k = 0; k < nt; ++k) {
-                const int4 bx = hdr->box[k];
-                const int pitch = pv.w_base + pv.w_step * (bx.z >> 16);
-                const uint32_t bk = base + bx.w + (uint32_t)((warp * pitch + lane) * PB);
-                const int4 *ofs = reinterpret_cast<const int4 *>(hdr->offs[k]);
+            const uint32_t lane_base = stage0 + (uint32_t)slot * STAGE_BYTES + (uint32_t)lane * PB;
+            uint32_t rec = hdr_a + (uint32_t)offsetof(StageRec, img);
+            for (int k = 0; k < nt; ++k, rec += (uint32_t)sizeof(ImageRec)) {
+                const int2 ir = lds_v2<0>(rec);   // {slot_off, pitch_bytes}
+                const uint32_t bk = lane_base + (uint32_t)ir.x + (uint32_t)(warp * ir.y);
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
-                    const int4 o = ofs[j4];
+                    const int4 o = (j4 == 0) ? lds_v4<16>(rec) : ((j4 == 1) ? lds_v4<32>(rec) : ((j4 == 2) ? lds_v4<48>(rec) : lds_v4<64>(rec)));
+                    static_assert(TG <= 16, "offset loads above cover 16 candidates");
                     const int off[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
