@@ -90,11 +90,20 @@ KB_EXPORT int kb_generate_psi_phi(const float *sci, const float *var, int H, int
 /* ---- psi/phi stack (psi_phi_array.cpp, PsiPhiArray) ---------------------------------------------- */
 /* StackSearch ctor (stack_search.cpp:37-75) -> fill_psi_phi_array_from_image_arrays (psi_phi_array.cpp:374-410).
  * sci/var: T pointers to H*W float32 images; psf: T pointers to psf_dim[t]^2 float32 kernels;
- * num_bytes in {-1, 4, 2, 1}. Builds psi/phi and the encoded array on the device, keeps a host copy in the
- * reference layout [t][row][col][psi,phi]. */
+ * num_bytes in {-1, 4, 2, 1}. Builds psi/phi and the encoded array on the device and leaves the search copy there
+ * (kb_on_gpu still reports 0 until kb_preload, like the reference; kb_unload frees it); the host copy in the
+ * reference layout [t][row][col][psi,phi] is filled by a background thread that every reader joins. */
 KB_EXPORT int kb_create_from_images(const float *const *sci, const float *const *var, const float *const *psf,
                           const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
                           kb_handle *out);
+/* The same for rows [row_lo, row_hi) of every image only (no reference counterpart: the reference is single-GPU and
+ * always builds whole images).  A rank of the multi-GPU search needs psi/phi only for its band of start rows plus
+ * the candidates' reach; the convolution is local, so it uploads and convolves just those rows (plus the PSF radius)
+ * of the caller's full-size images.  float32 stacks only.  Searches on such a handle must stay inside its rows
+ * (kb_search checks), and it cannot be re-uploaded after kb_unload. */
+KB_EXPORT int kb_create_from_images_rows(const float *const *sci, const float *const *var, const float *const *psf,
+                               const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
+                               int row_lo, int row_hi, kb_handle *out);
 /* fill_psi_phi_array (psi_phi_array.cpp:321-372): from precomputed psi/phi images. */
 KB_EXPORT int kb_create_from_psi_phi(const float *const *psi, const float *const *phi, int T, int H, int W,
                            const double *zeroed_times, int num_bytes, kb_handle *out);

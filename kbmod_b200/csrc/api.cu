@@ -6,8 +6,11 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <memory>
+#include <mutex>
+#include <thread>
 
 #include "common.cuh"
 
@@ -66,6 +69,16 @@ struct kb_stack_s {
     std::vector<double> times;
     void *host_array = nullptr;  // reference layout [t][row][col][psi,phi]
     bool host_pinned = false;
+    // The constructor leaves the stack on the device and fills the host copy from a background thread; everything
+    // that reads the host copy joins it first (ensure_host).
+    std::thread host_thread;
+    std::atomic<bool> host_done{false};
+    std::string host_error;
+    void *d_raw = nullptr;        // reference-layout bytes on the device while the background copy drains them
+    cudaStream_t host_stream = nullptr;
+    bool dev_cache = false;       // d_search / d_screen hold the whole canonical stack (built by the constructor)
+    int row_lo = 0, row_hi = 0;   // rows of every image this handle holds (the whole image unless band-limited)
+    bool keep_raw = false;        // enough HBM to keep d_raw for good (psi/phi curves are gathered from it)
     void *d_search = nullptr;  // canonical pitched search copy
     uint32_t *d_screen = nullptr;  // 16-bit fixed-point screening copy of the same pixels (StackView::screen)
     float q_step_psi = 1.0f, q_step_phi = 1.0f;  // its quantisation steps; known once the stack's value range is
@@ -116,11 +129,85 @@ static StackView make_view(kb_handle h) {
     return sv;
 }
 
-// The host copy is page-locked so uploads run at PCIe speed and the device can read it through UVA.
-// cudaHostAlloc faults the pages in one by one from a single thread (2.6 GB/s measured: 5 s for C4's 13.4 GB);
-// touching the pages first from all host threads and then registering the range is several times faster.
+// ---- pinned staging rings ------------------------------------------------------------------------------------
+// Caller-owned images and the host copy of the stack are ordinary pageable memory.  The driver moves such memory
+// through one internal bounce buffer with a single-threaded memcpy (10 GB/s here); a small ring of page-locked slots
+// filled (or drained) by all host threads keeps the PCIe link busy instead.  One ring per direction and device.
+struct PinnedRing {
+    static constexpr int kSlots = 4;
+    static constexpr size_t kSlotBytes = 8u << 20;
+    void *slot[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+    bool busy[kSlots] = {false, false, false, false};
+    int next = 0;
+    std::mutex mu;
+    void init() {
+        if (slot[0]) return;
+        for (int i = 0; i < kSlots; ++i) {
+            KB_CUDA(cudaHostAlloc(&slot[i], kSlotBytes, cudaHostAllocPortable));
+            KB_CUDA(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+        }
+    }
+};
+static PinnedRing g_ring_up[64], g_ring_down[64];
+
+static void parallel_memcpy(void *dst, const void *src, size_t n) {
+    const size_t piece = 256u << 10;
+    const long long np = (long long)((n + piece - 1) / piece);
+    if (np <= 2) {
+        memcpy(dst, src, n);
+        return;
+    }
+#pragma omp parallel for schedule(static)
+    for (long long i = 0; i < np; ++i) {
+        const size_t o = (size_t)i * piece;
+        memcpy((char *)dst + o, (const char *)src + o, std::min(piece, n - o));
+    }
+}
+
+// pageable host -> device, asynchronous with respect to `st` (returns when the last slot has been filled)
+static void ring_h2d(int device, void *d_dst, const void *h_src, size_t bytes, cudaStream_t st) {
+    PinnedRing &r = g_ring_up[device & 63];
+    std::lock_guard<std::mutex> lock(r.mu);
+    r.init();
+    for (size_t off = 0; off < bytes; off += PinnedRing::kSlotBytes) {
+        const size_t n = std::min(PinnedRing::kSlotBytes, bytes - off);
+        const int i = r.next;
+        r.next = (i + 1) % PinnedRing::kSlots;
+        if (r.busy[i]) KB_CUDA(cudaEventSynchronize(r.ev[i]));
+        parallel_memcpy(r.slot[i], (const char *)h_src + off, n);
+        KB_CUDA(cudaMemcpyAsync((char *)d_dst + off, r.slot[i], n, cudaMemcpyHostToDevice, st));
+        KB_CUDA(cudaEventRecord(r.ev[i], st));
+        r.busy[i] = true;
+    }
+}
+
+// device -> pageable host through the ring; synchronous (the data is in h_dst on return)
+static void ring_d2h(int device, void *h_dst, const void *d_src, size_t bytes, cudaStream_t st) {
+    PinnedRing &r = g_ring_down[device & 63];
+    std::lock_guard<std::mutex> lock(r.mu);
+    r.init();
+    const size_t S = PinnedRing::kSlotBytes;
+    const size_t nchunks = (bytes + S - 1) / S;
+    auto issue = [&](size_t c) {
+        const int i = (int)(c % PinnedRing::kSlots);
+        KB_CUDA(cudaMemcpyAsync(r.slot[i], (const char *)d_src + c * S, std::min(S, bytes - c * S), cudaMemcpyDeviceToHost, st));
+        KB_CUDA(cudaEventRecord(r.ev[i], st));
+    };
+    const size_t depth = PinnedRing::kSlots - 1;
+    for (size_t c = 0; c < std::min(depth, nchunks); ++c) issue(c);
+    for (size_t c = 0; c < nchunks; ++c) {
+        const int i = (int)(c % PinnedRing::kSlots);
+        KB_CUDA(cudaEventSynchronize(r.ev[i]));
+        parallel_memcpy((char *)h_dst + c * S, r.slot[i], std::min(S, bytes - c * S));
+        if (c + depth < nchunks) issue(c + depth);
+    }
+}
+
+// The host copy: ordinary memory, first touched by all host threads.  It is page-locked (cudaHostRegister) only when
+// a search has to upload it (pin_host_array): registering costs about 0.25 s per GB and most stacks never need it,
+// because the constructor leaves the stack on the device.
 static void alloc_host_array(kb_handle h, size_t bytes) {
-    const char *nopin = getenv("KB_NO_PIN");
     void *p = nullptr;
     if (posix_memalign(&p, 4096, std::max<size_t>(bytes, 4096)) != 0 || !p)
         throw Error("Unable to allocate space for CPU PsiPhi array.");
@@ -130,9 +217,23 @@ static void alloc_host_array(kb_handle h, size_t bytes) {
     for (long long i = 0; i < npages; ++i) c[(size_t)i * 4096] = 0;  // first touch
     h->host_array = p;
     h->host_pinned = false;
-    if (!(nopin && nopin[0] == '1')) {
-        if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) h->host_pinned = true;
-        else cudaGetLastError();
+}
+
+static void pin_host_array(kb_handle h) {
+    if (h->host_pinned || !h->host_array) return;
+    const char *nopin = getenv("KB_NO_PIN");
+    if (nopin && nopin[0] == '1') return;
+    if (cudaHostRegister(h->host_array, h->meta.total_array_size, cudaHostRegisterDefault) == cudaSuccess) h->host_pinned = true;
+    else cudaGetLastError();
+}
+
+// Everything that reads (or frees) the host copy waits for the background thread that fills it.
+static void ensure_host(kb_handle h) {
+    if (h->host_thread.joinable()) h->host_thread.join();
+    if (!h->host_error.empty()) {
+        const std::string e = h->host_error;
+        h->host_error.clear();
+        throw Error("building the host copy of the psi/phi stack failed: " + e);
     }
 }
 
@@ -177,32 +278,46 @@ static void scale_from_minmax(float mn, float mx, int nb, float out[3]) {
     out[2] = scale;
 }
 
-// Given the float2 psi/phi stack on the device (reference order, unpitched), produce the host array in the
-// requested encoding (fill_psi_phi_array, psi_phi_array.cpp:321-372).
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+static void set_screen_steps(kb_handle h, float amax_psi, float amax_phi);
+
+// Given the float2 psi/phi stack on the device (reference order, unpitched; rows [row_lo, row_hi) of every image are
+// valid), finish the handle (fill_psi_phi_array, psi_phi_array.cpp:321-372): scale parameters and codes for encoded
+// stacks, the canonical search copy and the screening copy -- both stay on the device -- and, in the background, the
+// host copy in the reference layout.  Takes ownership of d_pairs.
 static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
     const uint64_t npix = (uint64_t)h->T * h->H * h->W;
-    const double t_a = now_s();
-    alloc_host_array(h, h->meta.total_array_size);
-    if (getenv("KB_DEBUG"))
-        fprintf(stderr, "[kbmod_b200] host array (%s, %.2f GB) allocated in %.3f s\n", h->host_pinned ? "pinned" : "pageable",
-                h->meta.total_array_size / 1e9, now_s() - t_a);
+    const bool band = h->row_lo != 0 || h->row_hi != h->H;
+    const int r0 = h->row_lo, nr = h->row_hi - h->row_lo;
+    const size_t pb = 2 * (size_t)h->nb, rows = (size_t)h->T * h->H;
+    cudaStream_t st = h->stream;
+    h->times.assign(times, times + h->T);
+    KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
+    KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
+    KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
+    KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, st));
+    const char *nozm = getenv("KB_NO_ZERO_MARKER");
+    DevBuf<uint32_t> d_scan;
+    d_scan.ensure(5);
+    uint32_t scan[5];
+    launch_scan_raw_rows(d_pairs, h->T, h->H, r0, nr, h->W, d_scan.p, st);
+    KB_CUDA(cudaMemcpyAsync(scan, d_scan.p, sizeof(scan), cudaMemcpyDeviceToHost, st));
+    KB_CUDA(cudaStreamSynchronize(st));
+    // min / max over the finite values of each channel; none at all: the reference keeps FLT_MAX / -FLT_MAX (:223-232)
+    float pmn = 3.402823466e+38F, pmx = -3.402823466e+38F, fmn = pmn, fmx = pmx;
+    if (scan[1] <= scan[2]) { pmn = ordered_to_float(scan[1]); pmx = ordered_to_float(scan[2]); }
+    if (scan[3] <= scan[4]) { fmn = ordered_to_float(scan[3]); fmx = ordered_to_float(scan[4]); }
+    void *d_ref = d_pairs;   // reference-layout bytes for the host copy
     if (h->nb == 4) {
-        KB_CUDA(cudaMemcpyAsync(h->host_array, d_pairs, h->meta.total_array_size, cudaMemcpyDeviceToHost, h->stream));
+        h->zm_known = (scan[0] || (nozm && nozm[0] == '1')) ? 0 : 1;
+        set_screen_steps(h, pmn <= pmx ? std::max(fabsf(pmn), fabsf(pmx)) : 0.0f,
+                         fmn <= fmx ? std::max(fabsf(fmn), fabsf(fmx)) : 0.0f);
     } else {
-        DevBuf<uint32_t> d_mm;
-        d_mm.ensure(4);
-        launch_minmax(d_pairs, npix, d_mm.p, h->stream);
-        uint32_t mm[4];
-        KB_CUDA(cudaMemcpyAsync(mm, d_mm.p, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
-        KB_CUDA(cudaStreamSynchronize(h->stream));
-        // No finite value at all: the reference keeps min = FLT_MAX, max = -FLT_MAX (:223-232).
-        float pmn = 3.402823466e+38F, pmx = -3.402823466e+38F, fmn = pmn, fmx = pmx;
-        if (mm[0] <= mm[1]) { pmn = ordered_to_float(mm[0]); pmx = ordered_to_float(mm[1]); }
-        if (mm[2] <= mm[3]) { fmn = ordered_to_float(mm[2]); fmx = ordered_to_float(mm[3]); }
+        if (band) throw Error("band-limited construction supports float32 stacks only (the scale of an encoded "
+                              "stack depends on every row)");
         float pp[3], fp[3];
         scale_from_minmax(pmn, pmx, h->nb, pp);
         scale_from_minmax(fmn, fmx, h->nb, fp);
@@ -211,14 +326,75 @@ static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
         if (fp[0] > fp[1]) throw Error("Min value needs to be < max value. Got " + std::to_string(fp[0]) + " and " + std::to_string(fp[1]));
         h->meta.psi_min_val = pp[0]; h->meta.psi_max_val = pp[1]; h->meta.psi_scale = pp[2];
         h->meta.phi_min_val = fp[0]; h->meta.phi_max_val = fp[1]; h->meta.phi_scale = fp[2];
-        DevBuf<uint8_t> d_enc;
-        d_enc.ensure(h->meta.total_array_size);
-        launch_encode(d_pairs, npix, h->nb, pp, fp, d_enc.p, h->stream);
-        KB_CUDA(cudaMemcpyAsync(h->host_array, d_enc.p, h->meta.total_array_size, cudaMemcpyDeviceToHost, h->stream));
-        KB_CUDA(cudaStreamSynchronize(h->stream));
+        void *d_enc = nullptr;
+        KB_CUDA(cudaMalloc(&d_enc, h->meta.total_array_size));
+        launch_encode(d_pairs, npix, h->nb, pp, fp, d_enc, st);
+        d_ref = d_enc;
+        h->zm_known = 0;
+        set_screen_steps(h, std::max(fabsf(pp[0]), fabsf(pp[1])), std::max(fabsf(fp[0]), fabsf(fp[1])));
     }
-    KB_CUDA(cudaStreamSynchronize(h->stream));
-    h->times.assign(times, times + h->T);
+    h->zero_marker = h->zm_known;
+    launch_canonicalise_rows(d_ref, h->W, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0, nr, st);
+    launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
+                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, r0,
+                         nr, st);
+    KB_CUDA(cudaStreamSynchronize(st));
+    if (d_ref != d_pairs) cudaFree(d_pairs);
+    h->d_raw = d_ref;
+    const char *nocache = getenv("KB_NO_DEVICE_CACHE");
+    h->dev_cache = !(nocache && nocache[0] == '1');
+    {   // the reference-layout bytes stay on the device too while HBM is plentiful (180 GB): get_all_psi_phi_curves
+        // gathers from them (psi and phi validity are independent there, unlike in the canonical search copy)
+        size_t free_b = 0, total_b = 0;
+        const char *drop = getenv("KB_DROP_RAW");
+        h->keep_raw = h->dev_cache && !(drop && drop[0] == '1') && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
+                      free_b > 4 * (size_t)h->meta.total_array_size;
+    }
+    // ---- the host copy, off the caller's critical path ----
+    KB_CUDA(cudaStreamCreateWithFlags(&h->host_stream, cudaStreamNonBlocking));
+    const double t0 = now_s();
+    h->host_thread = std::thread([h, t0, r0, nr, pb]() {
+        try {
+            KB_CUDA(cudaSetDevice(h->device));
+            alloc_host_array(h, h->meta.total_array_size);
+            const size_t img = (size_t)h->H * h->W * pb;
+            if (nr == h->H) {
+                ring_d2h(h->device, h->host_array, h->d_raw, (size_t)h->T * img, h->host_stream);
+            } else {
+                for (int t = 0; t < h->T; ++t) {
+                    const size_t off = (size_t)t * img + (size_t)r0 * h->W * pb;
+                    ring_d2h(h->device, (char *)h->host_array + off, (const char *)h->d_raw + off, (size_t)nr * h->W * pb, h->host_stream);
+                }
+            }
+            if (getenv("KB_DEBUG"))
+                fprintf(stderr, "[kbmod_b200] host copy (%.2f GB) filled in the background in %.3f s\n",
+                        h->meta.total_array_size / 1e9, now_s() - t0);
+        } catch (const std::exception &e) {
+            h->host_error = e.what();
+        }
+        h->host_done.store(true);
+    });
+    if (!h->dev_cache) {   // no cache wanted: behave like the reference (host copy only)
+        ensure_host(h);
+        cudaFree(h->d_raw);
+        h->d_raw = nullptr;
+        cudaFree(h->d_search);
+        cudaFree(h->d_screen);
+        cudaFree(h->d_times);
+        h->d_search = nullptr;
+        h->d_screen = nullptr;
+        h->d_times = nullptr;
+    }
+}
+
+// The device-side source of the host copy is released as soon as the background copy is done and somebody looks.
+static void release_raw_if_done(kb_handle h, bool wait, bool force = false) {
+    if (wait) ensure_host(h);
+    if (!h->d_raw || (h->keep_raw && !force)) return;
+    if (!h->host_done.load()) return;   // still copying
+    ensure_host(h);
+    cudaFree(h->d_raw);
+    h->d_raw = nullptr;
 }
 
 static kb_handle new_handle() {
@@ -244,6 +420,7 @@ static void free_device_stack(kb_handle h, bool keep_alloc = false) {
         h->d_search = nullptr;
         h->d_screen = nullptr;
         h->d_times = nullptr;
+        h->dev_cache = false;
     }
     h->on_gpu = false;
 }
@@ -251,6 +428,9 @@ static void free_device_stack(kb_handle h, bool keep_alloc = false) {
 static void destroy_handle(kb_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
+    if (h->host_thread.joinable()) h->host_thread.join();
+    if (h->d_raw) cudaFree(h->d_raw);
+    if (h->host_stream) cudaStreamDestroy(h->host_stream);
     free_device_stack(h);
     if (h->host_array) {
         if (h->host_pinned) cudaHostUnregister(h->host_array);
@@ -287,6 +467,15 @@ static void set_screen_steps(kb_handle h, float amax_psi, float amax_phi) {
 // PsiPhiArray::move_to_gpu (psi_phi_array.cpp:74-111): upload + canonicalise into the pitched search copy.
 static void upload_stack(kb_handle h) {
     if (h->on_gpu) return;
+    if (h->dev_cache) {   // the copy the constructor built is still there: nothing to move
+        h->zero_marker = h->zm_known;
+        h->on_gpu = true;
+        return;
+    }
+    ensure_host(h);
+    if (h->row_lo != 0 || h->row_hi != h->H)
+        throw Error("a band-limited stack cannot be uploaded again after unload_psi_phi_array()");
+    pin_host_array(h);
     const size_t pb = pair_bytes(h->nb);
     const size_t rows = (size_t)h->T * h->H;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
@@ -343,7 +532,10 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     if (getenv("KB_DEBUG"))
         fprintf(stderr, "[kbmod_b200] pipelined upload? on_gpu=%d zm_known=%d pinned=%d\n", (int)h->on_gpu, h->zm_known,
                 (int)h->host_pinned);
-    if (h->on_gpu || h->zm_known < 0 || !h->q_known || !h->host_pinned) return false;
+    if (h->on_gpu || h->dev_cache || h->zm_known < 0 || !h->q_known) return false;
+    ensure_host(h);
+    pin_host_array(h);
+    if (!h->host_pinned) return false;
     const char *off = getenv("KB_NO_PIPELINED_UPLOAD");
     if (off && off[0] == '1') return false;
     const size_t pb = pair_bytes(h->nb);
@@ -504,66 +696,115 @@ int kb_generate_psi_phi(const float *sci, const float *var, int H, int W, const 
     KB_API_END
 }
 
+static void create_from_images(const float *const *sci, const float *const *var, const float *const *psf,
+                               const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
+                               int row_lo, int row_hi, kb_handle *out) {
+    if (T <= 0) throw Error("No images in the to process.");
+    kb_handle h = new_handle();
+    float2 *d_pairs = nullptr;
+    cudaStream_t copy_st = nullptr;
+    cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
+    auto cleanup = [&]() {
+        for (int i = 0; i < 2; ++i) {
+            if (copied[i]) cudaEventDestroy(copied[i]);
+            if (consumed[i]) cudaEventDestroy(consumed[i]);
+        }
+        if (copy_st) cudaStreamDestroy(copy_st);
+    };
+    try {
+        const double t_begin = now_s();
+        set_meta(h, num_bytes, T, H, W);
+        if (row_lo < 0 || row_hi > H || row_lo >= row_hi) throw Error("Invalid row range for the psi/phi stack.");
+        h->row_lo = row_lo;
+        h->row_hi = row_hi;
+        const size_t n = (size_t)H * W;
+        KB_CUDA(cudaMalloc(&d_pairs, sizeof(float2) * n * T));
+        // every PSF and its square (square_psf_values, image_utils_cpp.cpp:110-120) in one small upload
+        std::vector<size_t> koff(T + 1, 0);
+        int rmax = 0;
+        for (int t = 0; t < T; ++t) {
+            const int dim = psf_dim[t];
+            if (dim <= 0 || (dim & 1) == 0) throw Error("PSF kernels must be square with an odd dimension.");
+            koff[t + 1] = koff[t] + (size_t)dim * dim;
+            rmax = std::max(rmax, (dim - 1) / 2);
+        }
+        std::vector<float> kall(2 * koff[T]);
+        std::vector<float> ksum(2 * (size_t)T);
+        for (int t = 0; t < T; ++t) {
+            const size_t kn = koff[t + 1] - koff[t];
+            float *k1 = kall.data() + 2 * koff[t], *k2 = k1 + kn;
+            for (size_t i = 0; i < kn; ++i) {
+                k1[i] = psf[t][i];
+                k2[i] = psf[t][i] * psf[t][i];
+            }
+            ksum[2 * t] = host_sum(k1, (int)kn);
+            ksum[2 * t + 1] = host_sum(k2, (int)kn);
+        }
+        DevBuf<float> d_k;
+        d_k.ensure(std::max<size_t>(kall.size(), 1));
+        KB_CUDA(cudaMemcpyAsync(d_k.p, kall.data(), kall.size() * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        // Input rows of image t that rows [row_lo, row_hi) of its psi/phi depend on: the band plus the PSF radius.
+        // Double-buffered staging: the upload of image t+1 (through the pinned ring) overlaps the convolution of t.
+        const size_t max_rows = (size_t)std::min(H, row_hi - row_lo + 2 * rmax);
+        DevBuf<float> d_sci[2], d_var[2];
+        KB_CUDA(cudaStreamCreateWithFlags(&copy_st, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            d_sci[i].ensure(max_rows * W);
+            d_var[i].ensure(max_rows * W);
+            KB_CUDA(cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming));
+            KB_CUDA(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
+        }
+        uint64_t h2d_bytes = 0;
+        for (int t = 0; t < T; ++t) {
+            const int b = t & 1;
+            const int dim = psf_dim[t], rad = (dim - 1) / 2;
+            const int in_lo = std::max(0, row_lo - rad), in_hi = std::min(H, row_hi + rad);
+            const size_t nin = (size_t)(in_hi - in_lo) * W;
+            if (t >= 2) KB_CUDA(cudaStreamWaitEvent(copy_st, consumed[b], 0));
+            ring_h2d(h->device, d_sci[b].p, sci[t] + (size_t)in_lo * W, nin * sizeof(float), copy_st);
+            ring_h2d(h->device, d_var[b].p, var[t] + (size_t)in_lo * W, nin * sizeof(float), copy_st);
+            h2d_bytes += 2 * nin * sizeof(float);
+            KB_CUDA(cudaEventRecord(copied[b], copy_st));
+            KB_CUDA(cudaStreamWaitEvent(h->stream, copied[b], 0));
+            const float *k1 = d_k.p + 2 * koff[t], *k2 = k1 + (koff[t + 1] - koff[t]);
+            // the uploaded rows are convolved as an image of their own; its first row is row in_lo of the frame
+            launch_psi_phi(d_sci[b].p, d_var[b].p, in_hi - in_lo, W, k1, k2, dim, ksum[2 * t], ksum[2 * t + 1],
+                           d_pairs + (size_t)t * n + (size_t)in_lo * W, nullptr, nullptr, h->stream, row_lo - in_lo,
+                           row_hi - in_lo);
+            KB_CUDA(cudaEventRecord(consumed[b], h->stream));
+        }
+        KB_CUDA(cudaStreamSynchronize(h->stream));   // kall / ksum and the staging buffers die with this scope
+        const double t_gen = now_s();
+        if (getenv("KB_DEBUG"))
+            fprintf(stderr, "[kbmod_b200] H2D (%.2f GB through the pinned ring) + psi/phi kernels: %.3f s\n", h2d_bytes / 1e9,
+                    t_gen - t_begin);
+        float2 *pairs = d_pairs;
+        d_pairs = nullptr;   // finish_stack owns it from here
+        finish_stack(h, pairs, zeroed_times);
+        if (getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] scale / encode / search + screening copies: %.3f s\n", now_s() - t_gen);
+    } catch (...) {
+        cleanup();
+        if (d_pairs) cudaFree(d_pairs);
+        destroy_handle(h);
+        throw;
+    }
+    cleanup();
+    *out = h;
+}
+
 int kb_create_from_images(const float *const *sci, const float *const *var, const float *const *psf,
                           const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
                           kb_handle *out) {
     KB_API_BEGIN
-    if (T <= 0) throw Error("No images in the to process.");
-    kb_handle h = new_handle();
-    try {
-        const double t_begin = now_s();
-        set_meta(h, num_bytes, T, H, W);
-        const size_t n = (size_t)H * W;
-        DevBuf<float2> d_pairs;
-        d_pairs.ensure(n * T);
-        // Double-buffered staging: the H2D copy of image t+1 overlaps the convolution of image t.
-        DevBuf<float> d_sci[2], d_var[2], d_k[2], d_k2[2];
-        cudaStream_t copy_st;
-        KB_CUDA(cudaStreamCreateWithFlags(&copy_st, cudaStreamNonBlocking));
-        cudaEvent_t copied[2], consumed[2];
-        for (int i = 0; i < 2; ++i) {
-            d_sci[i].ensure(n);
-            d_var[i].ensure(n);
-            KB_CUDA(cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming));
-            KB_CUDA(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
-        }
-        std::vector<float> k2;
-        for (int t = 0; t < T; ++t) {
-            const int b = t & 1;
-            const int dim = psf_dim[t];
-            if (dim <= 0 || (dim & 1) == 0) throw Error("PSF kernels must be square with an odd dimension.");
-            const size_t kn = (size_t)dim * dim;
-            k2.resize(kn);
-            for (size_t i = 0; i < kn; ++i) k2[i] = psf[t][i] * psf[t][i];
-            if (t >= 2) KB_CUDA(cudaStreamWaitEvent(copy_st, consumed[b], 0));
-            d_k[b].ensure(kn);
-            d_k2[b].ensure(kn);
-            KB_CUDA(cudaMemcpyAsync(d_sci[b].p, sci[t], n * sizeof(float), cudaMemcpyHostToDevice, copy_st));
-            KB_CUDA(cudaMemcpyAsync(d_var[b].p, var[t], n * sizeof(float), cudaMemcpyHostToDevice, copy_st));
-            KB_CUDA(cudaMemcpyAsync(d_k[b].p, psf[t], kn * sizeof(float), cudaMemcpyHostToDevice, copy_st));
-            KB_CUDA(cudaMemcpyAsync(d_k2[b].p, k2.data(), kn * sizeof(float), cudaMemcpyHostToDevice, copy_st));
-            KB_CUDA(cudaStreamSynchronize(copy_st));  // k2 is reused by the host next iteration
-            KB_CUDA(cudaEventRecord(copied[b], copy_st));
-            KB_CUDA(cudaStreamWaitEvent(h->stream, copied[b], 0));
-            launch_psi_phi(d_sci[b].p, d_var[b].p, H, W, d_k[b].p, d_k2[b].p, dim, host_sum(psf[t], (int)kn),
-                           host_sum(k2.data(), (int)kn), d_pairs.p + (size_t)t * n, nullptr, nullptr, h->stream);
-            KB_CUDA(cudaEventRecord(consumed[b], h->stream));
-        }
-        KB_CUDA(cudaStreamSynchronize(h->stream));
-        for (int i = 0; i < 2; ++i) {
-            cudaEventDestroy(copied[i]);
-            cudaEventDestroy(consumed[i]);
-        }
-        cudaStreamDestroy(copy_st);
-        const double t_gen = now_s();
-        if (getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] H2D + psi/phi kernels: %.3f s\n", t_gen - t_begin);
-        finish_stack(h, d_pairs.p, zeroed_times);
-        if (getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] encode + D2H to host copy: %.3f s\n", now_s() - t_gen);
-    } catch (...) {
-        destroy_handle(h);
-        throw;
-    }
-    *out = h;
+    create_from_images(sci, var, psf, psf_dim, T, H, W, zeroed_times, num_bytes, 0, H, out);
+    KB_API_END
+}
+
+int kb_create_from_images_rows(const float *const *sci, const float *const *var, const float *const *psf,
+                               const int *psf_dim, int T, int H, int W, const double *zeroed_times, int num_bytes,
+                               int row_lo, int row_hi, kb_handle *out) {
+    KB_API_BEGIN
+    create_from_images(sci, var, psf, psf_dim, T, H, W, zeroed_times, num_bytes, row_lo, row_hi, out);
     KB_API_END
 }
 
@@ -572,21 +813,27 @@ int kb_create_from_psi_phi(const float *const *psi, const float *const *phi, int
     KB_API_BEGIN
     if (T <= 0) throw Error("Trying to fill PsiPhi from empty vectors.");
     kb_handle h = new_handle();
+    float2 *d_pairs = nullptr;
     try {
         set_meta(h, num_bytes, T, H, W);
+        h->row_lo = 0;
+        h->row_hi = H;
         const size_t n = (size_t)H * W;
-        DevBuf<float2> d_pairs;
-        d_pairs.ensure(n * T);
+        KB_CUDA(cudaMalloc(&d_pairs, sizeof(float2) * n * T));
         DevBuf<float> d_a, d_b;
         d_a.ensure(n);
         d_b.ensure(n);
         for (int t = 0; t < T; ++t) {
-            KB_CUDA(cudaMemcpyAsync(d_a.p, psi[t], n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-            KB_CUDA(cudaMemcpyAsync(d_b.p, phi[t], n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-            launch_interleave(d_a.p, d_b.p, n, d_pairs.p + (size_t)t * n, h->stream);
+            ring_h2d(h->device, d_a.p, psi[t], n * sizeof(float), h->stream);
+            ring_h2d(h->device, d_b.p, phi[t], n * sizeof(float), h->stream);
+            launch_interleave(d_a.p, d_b.p, n, d_pairs + (size_t)t * n, h->stream);
         }
-        finish_stack(h, d_pairs.p, zeroed_times);
+        KB_CUDA(cudaStreamSynchronize(h->stream));
+        float2 *pairs = d_pairs;
+        d_pairs = nullptr;
+        finish_stack(h, pairs, zeroed_times);
     } catch (...) {
+        if (d_pairs) cudaFree(d_pairs);
         destroy_handle(h);
         throw;
     }
@@ -608,6 +855,8 @@ int kb_get_meta(kb_handle h, kb_meta *meta) {
 
 int kb_host_array(kb_handle h, const void **ptr, uint64_t *nbytes) {
     KB_API_BEGIN
+    use_device(h);
+    release_raw_if_done(h, true);
     *ptr = h->host_array;
     *nbytes = h->meta.total_array_size;
     KB_API_END
@@ -616,6 +865,10 @@ int kb_host_array(kb_handle h, const void **ptr, uint64_t *nbytes) {
 int kb_read_psi_phi(kb_handle h, uint64_t t, int row, int col, float out[2]) {
     KB_API_BEGIN
     out[0] = out[1] = NAN;
+    if (row >= 0 && col >= 0 && row < h->H && col < h->W && t < (uint64_t)h->T) {
+        use_device(h);
+        release_raw_if_done(h, true);
+    }
     if (!h->host_array || row < 0 || col < 0 || row >= h->H || col >= h->W || t >= (uint64_t)h->T) return 0;
     const uint64_t idx = 2 * (h->meta.pixels_per_image * t + (uint64_t)row * h->W + (uint64_t)col);
     if (h->nb == 4) {
@@ -650,6 +903,7 @@ int kb_unload(kb_handle h) {
     KB_API_BEGIN
     use_device(h);
     KB_CUDA(cudaStreamSynchronize(h->stream));
+    release_raw_if_done(h, true, true);   // from now on the host copy is the only one
     free_device_stack(h);
     KB_API_END
 }
@@ -689,8 +943,24 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     Timer t_total, t_h2d, t_prep, t_search, t_post;
     uint32_t launches = 0;
 
+    release_raw_if_done(h, false);
+    {   // band-limited stacks: every row the search can touch must be one the handle holds
+        double vmax = 0.0, tabs = 0.0;
+        for (uint64_t i = 0; i < n_cand; ++i) vmax = std::max(vmax, (double)fabsf(vy[i]));
+        for (double t : h->times) tabs = std::max(tabs, fabs(t));
+        const double R = std::min(ceil(vmax * tabs) + 1.0, 4.0e6);
+        const int need_lo = std::max(0, (int)std::max(-4.0e6, (double)p.y_start_min - R));
+        const int need_hi = std::min(h->H, (int)std::min(4.0e6, (double)p.y_start_max + R));
+        if ((h->row_lo != 0 || h->row_hi != h->H) && need_lo < need_hi && (need_lo < h->row_lo || need_hi > h->row_hi))
+            throw Error("this band-limited stack holds image rows [" + std::to_string(h->row_lo) + ", " +
+                        std::to_string(h->row_hi) + ") but the search reaches rows [" + std::to_string(need_lo) + ", " +
+                        std::to_string(need_hi) + ")");
+    }
     t_total.start(st);
     const bool was_on_gpu = h->on_gpu;
+    // the copy the constructor left on the device serves searches of a stack that is "not on the GPU" as well
+    const bool cached = !was_on_gpu && h->dev_cache;
+    if (cached) h->zero_marker = h->zm_known;
     // A stack brought up for this search only (possibly just the rows in reach) must not outlive the call, also
     // when the call fails half way.
     struct DropTransientStack {
@@ -704,12 +974,12 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
                 if (h->up.band_stream[i]) cudaStreamSynchronize(h->up.band_stream[i]);
             free_device_stack(h, true);
         }
-    } drop{h, !was_on_gpu};
+    } drop{h, !was_on_gpu && !cached};
     t_h2d.start(st);
     // Not preloaded: the stack comes up for this search only.  From the second search of a handle on, in row chunks
     // on a copy stream, and the tiled kernel follows the rows as they land.
     bool pipelined = false;
-    if (!was_on_gpu) {
+    if (!was_on_gpu && !cached) {
         uint64_t copied = h->meta.total_array_size;
         if (h->kernel_mode != 1) {
             // rows within reach of the start rows: |vy| * max|t| plus a tile, its padding and a margin
@@ -900,12 +1170,18 @@ int kb_psi_phi_curves(kb_handle h, const kb_trajectory *trjs, uint64_t n, float 
     if (n == 0) return 0;
     // The curves are read from the reference-layout array (psi and phi validity are independent there).
     // Pinned host memory is directly addressable by the device (UVA); otherwise stage a temporary copy.
-    DevBuf<uint8_t> d_raw;
-    const void *src = h->host_array;
-    if (!h->host_pinned) {
-        d_raw.ensure(h->meta.total_array_size);
-        KB_CUDA(cudaMemcpyAsync(d_raw.p, h->host_array, h->meta.total_array_size, cudaMemcpyHostToDevice, h->stream));
-        src = d_raw.p;
+    // Preferably the reference-layout bytes the constructor kept on the device; else pinned host memory through UVA;
+    // else a temporary upload.
+    DevBuf<uint8_t> d_tmp_raw;
+    const void *src = h->d_raw;
+    if (!src) {
+        ensure_host(h);
+        src = h->host_array;
+        if (!h->host_pinned) {
+            d_tmp_raw.ensure(h->meta.total_array_size);
+            KB_CUDA(cudaMemcpyAsync(d_tmp_raw.p, h->host_array, h->meta.total_array_size, cudaMemcpyHostToDevice, h->stream));
+            src = d_tmp_raw.p;
+        }
     }
     DevBuf<kb_trajectory> d_t;
     DevBuf<float> d_out;

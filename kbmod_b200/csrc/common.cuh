@@ -136,9 +136,13 @@ float tiled_plan_kernel_ms(TiledPlan *plan);  // duration of the gather kernel o
 int launch_convolve(const float *d_img, int H, int W, const float *d_psf, int dim, float psf_total, float *d_out,
                     cudaStream_t st);
 // psi/phi for one image, written interleaved (float2) at d_out_pairs[H*W]; or to separate planes.
+// Only output rows [y_write_lo, y_write_hi) are written (band-limited construction: the other rows of the input are
+// the convolution's halo); y_write_hi < 0 = all rows.
 int launch_psi_phi(const float *d_sci, const float *d_var, int H, int W, const float *d_psf, const float *d_psf2,
                    int dim, float psf_total, float psf2_total, float2 *d_out_pairs, float *d_psi_plane,
-                   float *d_phi_plane, cudaStream_t st);
+                   float *d_phi_plane, cudaStream_t st, int y_write_lo = 0, int y_write_hi = -1);
+// zero-pair flag + per-channel min/max of rows [r0, r0 + nr) of a float stack in reference order: d_out[5]
+int launch_scan_raw_rows(const float2 *d_pairs, int T, int H, int r0, int nr, int W, uint32_t *d_out, cudaStream_t st);
 int launch_interleave(const float *d_psi, const float *d_phi, uint64_t n, float2 *d_out, cudaStream_t st);
 // min/max over finite values of both channels: d_mm = {psi_min, psi_max, phi_min, phi_max} as ordered uints.
 int launch_minmax(const float2 *d_pairs, uint64_t n, uint32_t *d_mm, cudaStream_t st);

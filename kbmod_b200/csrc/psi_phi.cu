@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
         conv_kernel(const float *__restrict__ in0, const float *__restrict__ in1, int H, int W,
                     const float *__restrict__ psf, const float *__restrict__ psf2, int dim, float psf_total,
                     float psf2_total, float2 *__restrict__ out_pairs, float *__restrict__ out0,
-                    float *__restrict__ out1) {
+                    float *__restrict__ out1, int y_write_lo, int y_write_hi) {
     extern __shared__ float smem[];
     const int rad = (dim - 1) / 2;
     const int tw = CT_X + 2 * rad, th = CT_Y + 2 * rad;
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(CT_X *CT_Y)
     __syncthreads();
 
     const int x = blockIdx.x * CT_X + threadIdx.x, y = blockIdx.y * CT_Y + threadIdx.y;
-    if (x >= W || y >= H) return;
+    if (x >= W || y >= H || y < y_write_lo || y >= y_write_hi) return;  // rows outside the wanted band: halo only
     const int cx = threadIdx.x + rad, cy = threadIdx.y + rad;
     const float ca = s_a[cy * tw + cx];
     float ra, rb = 0.0f;
@@ -125,21 +125,22 @@ int launch_convolve(const float *d_img, int H, int W, const float *d_psf, int di
     if (smem > 48 * 1024)
         KB_CUDA(cudaFuncSetAttribute(conv_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     conv_kernel<0><<<grid, block, smem, st>>>(d_img, nullptr, H, W, d_psf, nullptr, dim, psf_total, 0.0f, nullptr,
-                                              d_out, nullptr);
+                                              d_out, nullptr, 0, H);
     KB_CUDA(cudaGetLastError());
     return 1;
 }
 
 int launch_psi_phi(const float *d_sci, const float *d_var, int H, int W, const float *d_psf, const float *d_psf2,
                    int dim, float psf_total, float psf2_total, float2 *d_out_pairs, float *d_psi_plane,
-                   float *d_phi_plane, cudaStream_t st) {
+                   float *d_phi_plane, cudaStream_t st, int y_write_lo, int y_write_hi) {
+    if (y_write_hi < 0) y_write_hi = H;
     dim3 grid((W + CT_X - 1) / CT_X, (H + CT_Y - 1) / CT_Y), block(CT_X, CT_Y);
     const size_t smem = conv_smem(1, dim);
     if (smem > 220 * 1024) throw Error("PSF kernel too large for the convolution tile.");
     if (smem > 48 * 1024)
         KB_CUDA(cudaFuncSetAttribute(conv_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     conv_kernel<1><<<grid, block, smem, st>>>(d_sci, d_var, H, W, d_psf, d_psf2, dim, psf_total, psf2_total,
-                                              d_out_pairs, d_psi_plane, d_phi_plane);
+                                              d_out_pairs, d_psi_plane, d_phi_plane, y_write_lo, y_write_hi);
     KB_CUDA(cudaGetLastError());
     return 1;
 }
@@ -212,6 +213,59 @@ int launch_minmax(const float2 *d_pairs, uint64_t n, uint32_t *d_mm, cudaStream_
     return 1;
 }
 
+// The kernels below visit rows [r0, r0 + nr) of each of the T images of H rows (the whole stack: r0 = 0, nr = H).
+__device__ __forceinline__ uint64_t stack_row(uint64_t r, int H, int r0, int nr) {
+    return (r / (uint64_t)nr) * (uint64_t)H + (uint64_t)r0 + r % (uint64_t)nr;
+}
+
+// One pass over rows [r0, r0 + nr) of every image of a freshly built float stack (reference order, unpitched):
+// out[0] = 1 when some pair with both values finite is exactly (0, 0) (then invalid pairs cannot be stored as zeros),
+// out[1..4] = {psi_min, psi_max, phi_min, phi_max} over the finite values of each channel, as ordered uints.
+__global__ void scan_raw_rows_kernel(const float2 *__restrict__ pairs, int T, int H, int r0, int nr, int W,
+                                     uint32_t *out) {
+    const uint64_t total = (uint64_t)T * nr * (uint64_t)W;
+    uint32_t mn0 = 0xffffffffu, mx0 = 0u, mn1 = 0xffffffffu, mx1 = 0u;
+    bool hit = false;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const float2 v = pairs[stack_row(i / W, H, r0, nr) * (uint64_t)W + i % W];
+        const bool fa = isfinite(v.x), fb = isfinite(v.y);
+        if (fa) {
+            const uint32_t o = float_to_ordered(v.x);
+            mn0 = min(mn0, o);
+            mx0 = max(mx0, o);
+        }
+        if (fb) {
+            const uint32_t o = float_to_ordered(v.y);
+            mn1 = min(mn1, o);
+            mx1 = max(mx1, o);
+        }
+        hit |= fa && fb && v.x == 0.0f && v.y == 0.0f;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        mn0 = min(mn0, __shfl_xor_sync(0xffffffffu, mn0, d));
+        mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, d));
+        mn1 = min(mn1, __shfl_xor_sync(0xffffffffu, mn1, d));
+        mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, d));
+    }
+    const bool any_hit = __any_sync(0xffffffffu, hit);
+    if ((threadIdx.x & 31) == 0) {
+        if (any_hit) atomicExch(out, 1u);
+        atomicMin(out + 1, mn0);
+        atomicMax(out + 2, mx0);
+        atomicMin(out + 3, mn1);
+        atomicMax(out + 4, mx1);
+    }
+}
+
+int launch_scan_raw_rows(const float2 *d_pairs, int T, int H, int r0, int nr, int W, uint32_t *d_out, cudaStream_t st) {
+    const uint32_t init[5] = {0u, 0xffffffffu, 0u, 0xffffffffu, 0u};
+    KB_CUDA(cudaMemcpyAsync(d_out, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    if (nr > 0) scan_raw_rows_kernel<<<148 * 8, 256, 0, st>>>(d_pairs, T, H, r0, nr, W, d_out);
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
 // ---- quantiser (psi_phi_array_ds.h:40-43, psi_phi_array.cpp:264-291) --------------------------------
 __device__ __forceinline__ unsigned encode_value(float v, float mn, float safe_mx, float scale) {
     if (!isfinite(v)) return 0u;
@@ -273,11 +327,6 @@ template <>
 __device__ __forceinline__ ushort2 invalid_pair<ushort2>() { return make_ushort2(0, 0); }
 template <>
 __device__ __forceinline__ uchar2 invalid_pair<uchar2>() { return make_uchar2(0, 0); }
-
-// The kernels below visit rows [r0, r0 + nr) of each of the T images of H rows (the whole stack: r0 = 0, nr = H).
-__device__ __forceinline__ uint64_t stack_row(uint64_t r, int H, int r0, int nr) {
-    return (r / (uint64_t)nr) * (uint64_t)H + (uint64_t)r0 + r % (uint64_t)nr;
-}
 
 template <typename T2>
 __global__ void canonicalise_kernel(const T2 *src, int src_pitch, T2 *dst, int T, int H, int r0, int nr, int W, int Wp) {

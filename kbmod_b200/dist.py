@@ -30,6 +30,16 @@ def row_bands(y_min, y_max, world):
     return [(edges[k], edges[k + 1]) for k in range(world)]
 
 
+def band_rows(band, vy, zeroed_times, height, margin=2):
+    """Image rows [lo, hi) a rank needs psi/phi for when it searches the start rows ``band`` = (y0, y1) with candidate
+    y-velocities ``vy``: the band plus the candidates' reach max|vy| * max|t| (``StackSearch(..., rows=...)`` adds the
+    PSF radius for the convolution's inputs itself)."""
+    vmax = float(np.max(np.abs(np.asarray(vy, dtype=np.float32)))) if len(vy) else 0.0
+    tabs = float(np.max(np.abs(np.asarray(zeroed_times, dtype=np.float64)))) if len(zeroed_times) else 0.0
+    reach = int(np.ceil(vmax * tabs)) + 1 + margin
+    return max(0, band[0] - reach), min(int(height), band[1] + reach)
+
+
 def merge_sorted_lists(lists, top_n=0):
     """Host statement of the merge rule (used by the CPU tests and as documentation of the device merge):
     concatenate the per-rank lists in rank order and stable-sort by lh descending; keep the first top_n."""

@@ -309,8 +309,10 @@ def fill_psi_phi_array(result_data, num_bytes, psi_imgs, phi_imgs, zeroed_times)
     result_data._times = [float(t) for t in times]
 
 
-def fill_psi_phi_array_from_image_arrays(result_data, num_bytes, sci_imgs, var_imgs, psf_kernels, zeroed_times):
-    """psi_phi_array.cpp:374-410"""
+def fill_psi_phi_array_from_image_arrays(result_data, num_bytes, sci_imgs, var_imgs, psf_kernels, zeroed_times,
+                                         rows=None):
+    """psi_phi_array.cpp:374-410.  ``rows=(lo, hi)`` (extension, float32 stacks): build psi/phi for those image rows
+    only -- what one rank of the multi-GPU search needs (its band of start rows plus the candidates' reach)."""
     _lib.require_gpu()
     sci, var = _as_image_list(sci_imgs, "science"), _as_image_list(var_imgs, "variance")
     psfs = _as_image_list(psf_kernels, "PSF")
@@ -328,8 +330,13 @@ def fill_psi_phi_array_from_image_arrays(result_data, num_bytes, sci_imgs, var_i
             raise RuntimeError("PSF kernels must be square.")
     times = np.ascontiguousarray(zeroed_times, dtype=np.float64)
     h = C.c_void_p()
-    check(lib.kb_create_from_images(ptr_array(sci), ptr_array(var), ptr_array(psfs), dims, C.c_int(len(sci)),
-                                    C.c_int(H), C.c_int(W), ptr(times), C.c_int(num_bytes), C.byref(h)))
+    if rows is None:
+        check(lib.kb_create_from_images(ptr_array(sci), ptr_array(var), ptr_array(psfs), dims, C.c_int(len(sci)),
+                                        C.c_int(H), C.c_int(W), ptr(times), C.c_int(num_bytes), C.byref(h)))
+    else:
+        check(lib.kb_create_from_images_rows(ptr_array(sci), ptr_array(var), ptr_array(psfs), dims, C.c_int(len(sci)),
+                                             C.c_int(H), C.c_int(W), ptr(times), C.c_int(num_bytes),
+                                             C.c_int(int(rows[0])), C.c_int(int(rows[1])), C.byref(h)))
     result_data._adopt(h)
     result_data._times = [float(t) for t in times]
 
@@ -520,9 +527,10 @@ def extract_all_trajectory_obs_count(trjs): return _extract(trjs, "obs_count", n
 
 # ---- StackSearch (stack_search.{h,cpp}) -----------------------------------------------------------------
 class StackSearch:
-    """``StackSearch(sci_imgs, var_imgs, psf_kernels, zeroed_times, num_bytes=-1)`` -- stack_search.cpp:37-75."""
+    """``StackSearch(sci_imgs, var_imgs, psf_kernels, zeroed_times, num_bytes=-1)`` -- stack_search.cpp:37-75.
+    ``rows=(lo, hi)`` is an extension for the multi-GPU shard (see ``dist.band_rows``)."""
 
-    def __init__(self, sci_imgs, var_imgs, psf_kernels, zeroed_times, num_bytes=-1):
+    def __init__(self, sci_imgs, var_imgs, psf_kernels, zeroed_times, num_bytes=-1, rows=None):
         self._log = Logging.getLogger("kbmod.search.run_search")
         sci, var, psfs = list(sci_imgs), list(var_imgs), list(psf_kernels)
         times = [float(t) for t in zeroed_times]
@@ -544,7 +552,7 @@ class StackSearch:
         self.set_default_parameters(num_bytes)
         timer = DebugTimer("preparing Psi and Phi images", self._log)
         self._ppa = PsiPhiArray()
-        fill_psi_phi_array_from_image_arrays(self._ppa, num_bytes, sci, var, psfs, times)
+        fill_psi_phi_array_from_image_arrays(self._ppa, num_bytes, sci, var, psfs, times, rows)
         self._preloaded = False
         self._result_cache = None
         timer.stop()
@@ -626,9 +634,9 @@ class StackSearch:
             self._preloaded = True
 
     def unload_psi_phi_array(self):
-        if self._ppa.on_gpu:
-            self._ppa.clear_from_gpu()
-            self._preloaded = False
+        # also frees the copy the constructor left on the device when the stack was never "moved to the GPU"
+        self._ppa.clear_from_gpu()
+        self._preloaded = False
 
     def psi_phi_array_on_gpu(self):
         return self._ppa.on_gpu
