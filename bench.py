@@ -104,6 +104,62 @@ def make_inputs(c, n_gpus):
     return ds.stack_py, vx, vy
 
 
+class BandStack:
+    pass
+
+
+def make_band_inputs(c, need_rows):
+    """Inputs of config `c` for the image rows [need_rows[0], need_rows[1]) only (what one rank of a strong-scaling run
+    reads: its band of start rows + the candidates' reach + the PSF radius).  Every (image, 64-row block) has its own
+    seeded generator and the movers come from one shared generator, so ranks that need different rows see the same
+    frames without any of them generating a whole 13 GB stack.  The arrays are full-size (the C-ABI takes whole
+    images); rows outside `need_rows` are never written, and never read."""
+    from kbmod_b200 import fake_data as fd
+    T, H, W, noise = c["T"], c["H"], c["W"], 2.0
+    times = np.asarray(fd.create_fake_times(T, 57130.2, obs_per_day=c["obs_per_day"],
+                                            intra_night_gap=c.get("intra", 0.01)), dtype=float)
+    zeroed = times - times[0]
+    psf = fd.make_gaussian_kernel(c["psf"])
+    gen = fd.VelocityGridSearch(*c["grid"]) if "grid" in c else fd.EclipticCenteredSearch(*c["ecliptic"])
+    vx, vy = gen.to_arrays()
+    lo, hi = max(0, need_rows[0]), min(H, need_rows[1])
+    B = 64
+    sci = [np.empty((H, W), dtype=np.float32) for _ in range(T)]
+    var = [np.empty((H, W), dtype=np.float32) for _ in range(T)]
+    for t in range(T):
+        for b in range(lo // B, (hi + B - 1) // B):
+            r0, r1 = b * B, min((b + 1) * B, H)
+            rng = np.random.default_rng([c["seed"], t, b])
+            blk = rng.standard_normal((r1 - r0, W), dtype=np.float32) * np.float32(noise)
+            vblk = np.full((r1 - r0, W), noise * noise, dtype=np.float32)
+            if c["mask"] > 0:
+                m = rng.random((r1 - r0, W), dtype=np.float32) < c["mask"]
+                blk[m] = np.nan
+                vblk[m] = np.nan
+            a, e = max(r0, lo), min(r1, hi)
+            sci[t][a:e] = blk[a - r0:e - r0]
+            var[t][a:e] = vblk[a - r0:e - r0]
+    orng = np.random.default_rng([c["seed"], 9999])
+    rad = psf.shape[0] // 2
+    objects = []
+    for _ in range(c["n_obj"]):
+        k = int(orng.integers(0, len(vx)))
+        ox, oy = int(orng.random() * W), int(orng.random() * H)
+        objects.append((ox, oy, float(vx[k]), float(vy[k])))
+        for t in range(T):
+            x, y = int(ox + vx[k] * zeroed[t] + 0.5), int(oy + vy[k] * zeroed[t] + 0.5)
+            for dy in range(-rad, rad + 1):
+                yy = y + dy
+                if yy < lo or yy >= hi:
+                    continue
+                x0, x1 = max(0, x - rad), min(W, x + rad + 1)
+                if x0 < x1:
+                    sci[t][yy, x0:x1] += np.float32(500.0) * psf[dy + rad, x0 - (x - rad):x1 - (x - rad)]
+    st = BandStack()
+    st.sci, st.var, st.psfs, st.zeroed_times, st.objects = sci, var, [psf] * T, zeroed, objects
+    return st, vx, vy
+
+
 def configure(s, c, band=None):
     s.set_min_obs(c["min_obs"])
     s.set_results_per_pixel(c["K"])
@@ -322,6 +378,52 @@ def reference_gpu_leg(c, stack, vx, vy):
     return parity, timing
 
 
+def named_config_leg(kb, dist, comm, rank, world, c, name):
+    """BASELINE.json's own multi-GPU workload next to the weak-scaling curve: the named frame, its start-pixel rows
+    split over the ranks (strong scaling), each rank building psi/phi for its own rows only; construction, two
+    searches with the NCCL merge and the read-back of the merged list, timed from the host images on."""
+    H = c["H"]
+    band = tuple(dist.row_bands(0, H, world)[rank])
+    import kbmod_b200.fake_data as fd
+    times = np.asarray(fd.create_fake_times(c["T"], 57130.2, obs_per_day=c["obs_per_day"],
+                                            intra_night_gap=c.get("intra", 0.01)), dtype=float)
+    gen = fd.VelocityGridSearch(*c["grid"]) if "grid" in c else fd.EclipticCenteredSearch(*c["ecliptic"])
+    vy_all = gen.to_arrays()[1]
+    rows = dist.band_rows(band, vy_all, times - times[0], H)
+    rad = fd.make_gaussian_kernel(c["psf"]).shape[0] // 2
+    stack, vx, vy = make_band_inputs(c, (rows[0] - rad, rows[1] + rad))
+    comm.barrier()
+    t0 = time.perf_counter()
+    s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"], rows=rows)
+    ctor_s = time.perf_counter() - t0
+    configure(s, c, band)
+    s.search_all((vx, vy), True)
+    dist.merge_results(s, 0)
+    n = len(s.get_results_array())
+    first_ms = 1e3 * (time.perf_counter() - t0)
+    comm.barrier()
+    steps = 2
+    s.timer_start()
+    k_ms = 0.0
+    for _ in range(steps):
+        s.search_all((vx, vy), True)
+        dist.merge_results(s, 0)
+        k_ms += s.last_timing()["ms_main_kernel"]
+    ms = comm.max_float(s.timer_stop() / steps)
+    evals = c["W"] * H * len(vx) * c["T"]
+    rec = {"workload": workload_name(name, c, 1), "scaling": "strong", "n_gpus": world, "steps": steps,
+           "ms_per_step": ms, "value": evals / (ms * 1e-3), "unit": UNIT,
+           "gather_kernel_ms_slowest_rank": comm.max_float(k_ms / steps),
+           "ctor_seconds_slowest_rank": comm.max_float(ctor_s),
+           "ctor_plus_first_search_ms": comm.max_float(first_ms),
+           "ctor_plus_first_search_value": evals / (comm.max_float(first_ms) * 1e-3),
+           "results": int(n), "rows_per_rank": int(rows[1] - rows[0]),
+           "note": "every rank builds psi/phi for its band of start rows plus the candidates' reach only; inputs are "
+                   "generated per rank for those rows (seeded per 64-row block, same frames on every rank)"}
+    del s
+    return rec
+
+
 def run_ours(args, c, cfg_name):
     from kbmod_b200 import search as kb
     from kbmod_b200 import dist
@@ -350,8 +452,13 @@ def run_ours(args, c, cfg_name):
     # ---- one-shot pipeline, as KBMOD drives the API (run_search.py:363-378): construct, search once, read results --
     # Timed on the host clock from the first byte of the host images to the result list on the host; the device is
     # idle before and after.  `e2e_first_search` is the search + read part of the same pass.
+    # N > 1: every rank builds psi/phi only for the image rows its band of start rows can reach (float stacks; the
+    # scale of an encoded stack depends on every row, so those are built whole on every rank)
+    rows_held = None
+    if world > 1 and c["nb"] not in (1, 2):
+        rows_held = dist.band_rows(band, vy, stack.zeroed_times, c["H"] * frames)
     t0 = time.perf_counter()
-    s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"])
+    s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"], rows=rows_held)
     ctor_s = time.perf_counter() - t0
     configure(s, c, use_band)
     t1 = time.perf_counter()
@@ -482,17 +589,25 @@ def run_ours(args, c, cfg_name):
     if comm is not None:
         # NCCL-merged list of all ranks against one GPU searching the whole frame alone (rank 0, outside the timing)
         merged = results_digest(s.get_results_array())
+        line["ctor_seconds_max_over_ranks"] = comm.max_float(ctor_s)
         if rank == 0:
             ymin, ymax = (0, c["H"]) if strong else (0, c["H"] * world)
             if c.get("band_div") and not strong:
                 line["merge_check"] = "skipped (bands of a band_div config do not tile the frame)"
+            elif args.no_merge_check:
+                line["merge_check"] = "skipped (--no-merge-check)"
             else:
-                s.set_start_bounds_y(ymin, ymax)
-                s.search_all((vx, vy), True)
-                whole = results_digest(s.get_results_array())
+                sw_ = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"])   # the whole frame
+                configure(sw_, c, (ymin, ymax))
+                sw_.search_all((vx, vy), True)
+                whole = results_digest(sw_.get_results_array())
                 line["merge_check"] = "identical" if whole == merged else "differs"
-                line["merge_check_n"] = int(s.get_number_total_results())
+                line["merge_check_n"] = int(sw_.get_number_total_results())
+                del sw_
         comm.barrier()
+        if args.named_config and args.named_config in CONFIGS and not strong:
+            del s
+            line["named_config"] = named_config_leg(kb, dist, comm, rank, world, CONFIGS[args.named_config], args.named_config)
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -545,6 +660,9 @@ def main():
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the reference-GPU parity / timing leg")
+    ap.add_argument("--no-merge-check", action="store_true", help="N > 1: skip rank 0's whole-frame check of the merge")
+    ap.add_argument("--named-config", default="C4", help="N > 1 (weak runs): also run this config strong-scaled, "
+                    "construction included (BASELINE.json's multi-GPU workload); '' to skip")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every GPU searches its own copy-sized band of an N-times taller frame (default, "
                          "the driver's scaling run); strong = the named frame, start-pixel rows split over the GPUs "

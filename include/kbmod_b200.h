@@ -239,12 +239,18 @@ KB_EXPORT int kb_sort_trajectories_static(kb_trajectory *d_list, uint64_t n, voi
 
 /* ---- multi-GPU merge (no reference counterpart: the reference is single-GPU) ---------------------- */
 /* One process per GPU.  Rank 0 calls kb_nccl_unique_id and ships the 128 bytes to the other ranks by any
- * means; every rank then calls kb_nccl_init.  kb_search_merge_topn all-gathers every rank's sorted results
- * over NCCL and leaves the global best `top_n` (0 = all) as this handle's result list on every rank. */
+ * means; every rank then calls kb_nccl_init.  kb_merge_results_allgather all-gathers every rank's sorted results
+ * over NCCL and leaves the global best `top_n` (0 = all) as this handle's result list on every rank.  With
+ * top_n > 0 the host does not wait for anything before the gather (the counts travel in the blocks). */
 KB_EXPORT int kb_nccl_unique_id(uint8_t id[128]);
 KB_EXPORT int kb_nccl_init(const uint8_t id[128], int rank, int world_size);
 KB_EXPORT int kb_nccl_finalize(void);
 KB_EXPORT int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results);
+/* The merge kernel of kb_merge_results_allgather on one device, fed from host lists (each sorted by lh descending):
+ * out receives the first top_n (0 = all) records of the merged list, equal lh values in (list, position) order;
+ * *n_out their number.  out has room for min(top_n, sum of counts) records. */
+KB_EXPORT int kb_merge_sorted_lists(const kb_trajectory *const *lists, const uint64_t *counts, int n_lists,
+                                    uint64_t top_n, kb_trajectory *out, uint64_t *n_out);
 
 #ifdef __cplusplus
 }

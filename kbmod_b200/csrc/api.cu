@@ -212,9 +212,22 @@ static void alloc_host_array(kb_handle h, size_t bytes) {
     if (posix_memalign(&p, 4096, std::max<size_t>(bytes, 4096)) != 0 || !p)
         throw Error("Unable to allocate space for CPU PsiPhi array.");
     char *c = static_cast<char *>(p);
-    const long long npages = (long long)((bytes + 4095) / 4096);
+    const bool band = h->row_lo != 0 || h->row_hi != h->H;
+    if (!band) {
+        const long long npages = (long long)((bytes + 4095) / 4096);
 #pragma omp parallel for schedule(static)
-    for (long long i = 0; i < npages; ++i) c[(size_t)i * 4096] = 0;  // first touch
+        for (long long i = 0; i < npages; ++i) c[(size_t)i * 4096] = 0;  // first touch
+    } else {
+        // band-limited handle: only its rows are ever written; the other pages stay untouched (and uncommitted)
+        const size_t row_bytes = (size_t)h->W * 2 * h->nb, img = row_bytes * h->H;
+        for (int t = 0; t < h->T; ++t) {
+            char *b0 = c + (size_t)t * img + (size_t)h->row_lo * row_bytes;
+            const size_t nb = (size_t)(h->row_hi - h->row_lo) * row_bytes;
+            const long long npages = (long long)((nb + 4095) / 4096);
+#pragma omp parallel for schedule(static)
+            for (long long i = 0; i < npages; ++i) b0[std::min((size_t)i * 4096, nb - 1)] = 0;
+        }
+    }
     h->host_array = p;
     h->host_pinned = false;
 }
@@ -473,17 +486,25 @@ static void upload_stack(kb_handle h) {
         return;
     }
     ensure_host(h);
-    if (h->row_lo != 0 || h->row_hi != h->H)
-        throw Error("a band-limited stack cannot be uploaded again after unload_psi_phi_array()");
     pin_host_array(h);
     const size_t pb = pair_bytes(h->nb);
     const size_t rows = (size_t)h->T * h->H;
+    const int r0 = h->row_lo, nr = h->row_hi - h->row_lo;   // the rows this handle holds (all of them as a rule)
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
     if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
-    KB_CUDA(cudaMemcpy2DAsync(h->d_search, (size_t)h->Wp * pb, h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, rows,
-                              cudaMemcpyHostToDevice, h->stream));
+    {
+        cudaMemcpy3DParms q;
+        memset(&q, 0, sizeof(q));
+        q.srcPtr = make_cudaPitchedPtr(h->host_array, (size_t)h->W * pb, (size_t)h->W * pb, (size_t)h->H);
+        q.dstPtr = make_cudaPitchedPtr(h->d_search, (size_t)h->Wp * pb, (size_t)h->Wp * pb, (size_t)h->H);
+        q.srcPos = make_cudaPos(0, (size_t)r0, 0);
+        q.dstPos = make_cudaPos(0, (size_t)r0, 0);
+        q.extent = make_cudaExtent((size_t)h->W * pb, (size_t)nr, (size_t)h->T);
+        q.kind = cudaMemcpyHostToDevice;
+        KB_CUDA(cudaMemcpy3DAsync(&q, h->stream));
+    }
     h->zero_marker = 0;
     const char *nozm = getenv("KB_NO_ZERO_MARKER");
     if (h->nb == 4 && h->zm_known < 0) {
@@ -499,7 +520,8 @@ static void upload_stack(kb_handle h) {
     }
     if (h->nb != 4) h->zm_known = 0;
     h->zero_marker = h->zm_known;
-    launch_canonicalise(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, h->stream);
+    launch_canonicalise_rows(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0, nr,
+                             h->stream);
     if (!h->q_known) {
         // ... and how large do the values get: the quantisation steps of the screening copy
         if (h->nb == 4) {
@@ -520,8 +542,8 @@ static void upload_stack(kb_handle h) {
         }
     }
     launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
-                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, 0,
-                         h->H, h->stream);
+                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, r0,
+                         nr, h->stream);
     h->on_gpu = true;
 }
 
@@ -548,12 +570,13 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     if (bytes < min_bytes || h->H < 2 * UploadProgress::kMaxChunks) return false;
     // Only the rows this search can touch (its start rows plus the candidates' reach) are brought up: the copy is
     // dropped again after the search, so the rest of the stack is never read.  Too thin a range: take everything.
-    row_lo = std::max(0, std::min(row_lo, h->H));
-    row_hi = std::max(0, std::min(row_hi, h->H));
-    if (row_hi - row_lo < 2 * UploadProgress::kMaxChunks) {
-        row_lo = 0;
-        row_hi = h->H;
+    row_lo = std::max(h->row_lo, std::min(row_lo, h->row_hi));
+    row_hi = std::max(h->row_lo, std::min(row_hi, h->row_hi));
+    if (row_hi - row_lo < 2 * UploadProgress::kMaxChunks) {   // too thin a range: everything the handle holds
+        row_lo = h->row_lo;
+        row_hi = h->row_hi;
     }
+    if (row_hi - row_lo < 2 * UploadProgress::kMaxChunks) return false;
     const int64_t span = row_hi - row_lo;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
     if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
@@ -1252,6 +1275,40 @@ int kb_grid_filter(const kb_trajectory *trjs, uint64_t n, double bin_width, doub
     KB_API_END
 }
 
+// The merge step of the multi-GPU search on one device, from host lists (what kb_merge_results_allgather does with
+// the blocks ncclAllGather delivers): n_lists lists, each sorted by lh descending, merged into one; equal lh values
+// keep (list, position) order.
+int kb_merge_sorted_lists(const kb_trajectory *const *lists, const uint64_t *counts, int n_lists, uint64_t top_n,
+                          kb_trajectory *out, uint64_t *n_out) {
+    KB_API_BEGIN
+    if (n_lists <= 0 || !counts || !lists || !n_out) throw Error("kb_merge_sorted_lists: bad arguments");
+    uint64_t cap = 0, total = 0;
+    for (int r = 0; r < n_lists; ++r) {
+        cap = std::max(cap, counts[r]);
+        total += counts[r];
+    }
+    const uint64_t keep = (top_n && top_n < total) ? top_n : total;
+    *n_out = keep;
+    if (keep == 0) return 0;
+    const size_t hdr = (size_t)merge_header_bytes();
+    const size_t blk = (hdr + sizeof(kb_trajectory) * cap + 15) / 16 * 16;
+    DevBuf<uint8_t> d_blocks;
+    DevBuf<kb_trajectory> d_out, d_in;
+    DevBuf<uint64_t> d_total;
+    d_blocks.ensure(blk * n_lists);
+    d_out.ensure(keep);
+    d_in.ensure(std::max<uint64_t>(cap, 1));
+    d_total.ensure(1);
+    for (int r = 0; r < n_lists; ++r) {
+        if (counts[r]) KB_CUDA(cudaMemcpy(d_in.p, lists[r], sizeof(kb_trajectory) * counts[r], cudaMemcpyHostToDevice));
+        merge_pack_block(d_blocks.p + (size_t)r * blk, d_in.p, counts[r], 0);
+        KB_CUDA(cudaStreamSynchronize(0));
+    }
+    merge_sorted_runs(d_blocks.p, blk, n_lists, cap, d_out.p, keep, d_total.p, 0);
+    KB_CUDA(cudaMemcpy(out, d_out.p, sizeof(kb_trajectory) * keep, cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
 }  // extern "C"
 
 // ---- accessors used by nccl_merge.cu ------------------------------------------------------------------
@@ -1262,14 +1319,11 @@ kb_trajectory *handle_results(kb_handle h, uint64_t *n) {
     *n = h->n_results;
     return h->d_results.p;
 }
-void handle_replace_results(kb_handle h, const kb_trajectory *d_src, uint64_t n, bool sort) {
-    h->d_tmp.ensure(std::max<uint64_t>(n, 1));
-    if (d_src != h->d_results.p) {
-        h->d_results.ensure(std::max<uint64_t>(n, 1));
-        if (n) KB_CUDA(cudaMemcpyAsync(h->d_results.p, d_src, sizeof(kb_trajectory) * n, cudaMemcpyDeviceToDevice, h->stream));
-    }
-    if (sort) sort_trajectories_by_lh(h->d_results.p, n, h->scratch, h->d_tmp.p, h->stream);
-    KB_CUDA(cudaStreamSynchronize(h->stream));
-    h->n_results = n;
+// Room for `capacity` results in the handle's list (contents undefined afterwards); the caller fills it on the
+// handle's stream and then sets the count.
+kb_trajectory *handle_results_reserve(kb_handle h, uint64_t capacity) {
+    h->d_results.ensure(std::max<uint64_t>(capacity, 1));
+    return h->d_results.p;
 }
+void handle_set_result_count(kb_handle h, uint64_t n) { h->n_results = n; }
 }  // namespace kb

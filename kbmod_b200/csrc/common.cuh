@@ -187,7 +187,13 @@ int filter_finish(const Slot *d_slots, uint64_t n_slots, uint64_t n_keep, int K,
                   bool *invalid, cudaStream_t st);
 int slots_to_trajectories(const Slot *d_slots, uint64_t n_slots, int K, int sw, int x0, int y0, const float *d_vx,
                           const float *d_vy, kb_trajectory *d_out, cudaStream_t st);
-// Sort (key desc by lh) an existing device list of trajectories in place (used by the multi-GPU merge).
+// Multi-GPU merge (nccl_merge.cu): blocks of {32-byte header with the record count, sorted records}; every record
+// computes its own position in the merged list (stable with respect to block order).
+int merge_header_bytes();
+int merge_pack_block(void *d_block, const kb_trajectory *d_list, uint64_t n, cudaStream_t st);
+int merge_sorted_runs(const void *d_blocks, size_t block_bytes, int world, uint64_t cap_in, kb_trajectory *d_out,
+                      uint64_t keep, uint64_t *d_total, cudaStream_t st);
+// Sort (key desc by lh) an existing device list of trajectories in place.
 int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &scr, kb_trajectory *d_tmp,
                             cudaStream_t st);
 

@@ -1,9 +1,10 @@
 // nccl_merge.cu -- multi-GPU merge of per-GPU result lists (no reference counterpart; the reference is
 // single-GPU).  One process per GPU; start pixels are sharded by the caller (row bands via the start bounds),
 // psi/phi is replicated.  Every rank contributes its sorted list (optionally only its first top_n entries --
-// the global best N are always among the per-rank best N); ncclAllGather over NVLink moves the padded blocks,
-// then every rank compacts and re-sorts with the same stable radix sort as the single-GPU path, so ties keep
-// (rank, position) order == (y, x, slot) order and the merged list equals the single-GPU list.
+// the global best N are always among the per-rank best N); ncclAllGather over NVLink moves the padded blocks
+// (record count in each block's header), then every record computes its own position in the merged list from
+// binary searches in the other ranks' sorted runs (results.cu merge_runs_kernel).  Ties keep (rank, position)
+// order == (y, x, slot) order, so the merged list equals the single-GPU list.
 //
 // NCCL is bound at run time with dlopen so the library has no link-time dependency on it.
 #include <dlfcn.h>
@@ -15,7 +16,8 @@ namespace kb {
 cudaStream_t handle_stream(kb_handle h);
 int handle_device(kb_handle h);
 kb_trajectory *handle_results(kb_handle h, uint64_t *n);
-void handle_replace_results(kb_handle h, const kb_trajectory *d_src, uint64_t n, bool sort);
+kb_trajectory *handle_results_reserve(kb_handle h, uint64_t capacity);
+void handle_set_result_count(kb_handle h, uint64_t n);
 
 typedef struct { char internal[128]; } nccl_unique_id;
 typedef void *nccl_comm_t;
@@ -50,7 +52,7 @@ struct MergeBuf {
         return p;
     }
 };
-static MergeBuf g_counts, g_send, g_all, g_cat;
+static MergeBuf g_counts, g_send, g_all;
 
 static void nccl_load() {
     if (g_nccl.lib) return;
@@ -112,7 +114,7 @@ int kb_nccl_finalize(void) {
         KB_NCCL(g_nccl.CommDestroy(g_nccl.comm));
         g_nccl.comm = nullptr;
     }
-    for (MergeBuf *b : {&g_counts, &g_send, &g_all, &g_cat}) {
+    for (MergeBuf *b : {&g_counts, &g_send, &g_all}) {
         if (b->p) cudaFree(b->p);
         b->p = nullptr;
         b->cap = 0;
@@ -128,42 +130,36 @@ int kb_merge_results_allgather(kb_handle h, uint64_t top_n, uint64_t *n_results)
     const int world = g_nccl.world;
     uint64_t n_local = 0;
     kb_trajectory *d_local = handle_results(h, &n_local);
-    uint64_t n_send = (top_n && top_n < n_local) ? top_n : n_local;
+    const uint64_t n_send = (top_n && top_n < n_local) ? top_n : n_local;
+    const size_t hdr = (size_t)merge_header_bytes();
 
-    // 1. counts
-    uint64_t *d_counts = static_cast<uint64_t *>(g_counts.ensure(sizeof(uint64_t) * (world + 1)));
-    KB_CUDA(cudaMemcpyAsync(d_counts + world, &n_send, sizeof(uint64_t), cudaMemcpyHostToDevice, st));
-    KB_NCCL(g_nccl.AllGather(d_counts + world, d_counts, 1, NCCL_UINT64, g_nccl.comm, st));
-    std::vector<uint64_t> counts(world);
-    KB_CUDA(cudaMemcpyAsync(counts.data(), d_counts, sizeof(uint64_t) * world, cudaMemcpyDeviceToHost, st));
-    KB_CUDA(cudaStreamSynchronize(st));
-    uint64_t max_c = 0, total = 0;
-    for (uint64_t c : counts) { max_c = std::max(max_c, c); total += c; }
-
-    if (total == 0) {
-        handle_replace_results(h, d_local, 0, false);
-        if (n_results) *n_results = 0;
-        return 0;
+    // Records per block.  With a caller-supplied top_n no rank sends more than that, so nothing has to be known
+    // about the other ranks before the gather: the counts travel in the block headers and the host never waits.
+    // Without it the largest count is exchanged first (8 bytes per rank, one host wait).
+    uint64_t cap = top_n;
+    uint64_t *d_counts = static_cast<uint64_t *>(g_counts.ensure(sizeof(uint64_t) * (world + 2)));
+    if (!top_n) {
+        KB_CUDA(cudaMemcpyAsync(d_counts + world, &n_send, sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+        KB_NCCL(g_nccl.AllGather(d_counts + world, d_counts, 1, NCCL_UINT64, g_nccl.comm, st));
+        std::vector<uint64_t> counts(world);
+        KB_CUDA(cudaMemcpyAsync(counts.data(), d_counts, sizeof(uint64_t) * world, cudaMemcpyDeviceToHost, st));
+        KB_CUDA(cudaStreamSynchronize(st));
+        for (uint64_t c : counts) cap = std::max(cap, c);
     }
-    // 2. padded blocks
-    const size_t blk = sizeof(kb_trajectory) * max_c;
-    kb_trajectory *d_send = static_cast<kb_trajectory *>(g_send.ensure(blk));
-    kb_trajectory *d_all = static_cast<kb_trajectory *>(g_all.ensure(blk * world));
-    kb_trajectory *d_cat = static_cast<kb_trajectory *>(g_cat.ensure(sizeof(kb_trajectory) * total));
-    KB_CUDA(cudaMemsetAsync(d_send, 0, blk, st));
-    if (n_send) KB_CUDA(cudaMemcpyAsync(d_send, d_local, sizeof(kb_trajectory) * n_send, cudaMemcpyDeviceToDevice, st));
+    const size_t blk = (hdr + sizeof(kb_trajectory) * cap + 15) / 16 * 16;
+    uint8_t *d_send = static_cast<uint8_t *>(g_send.ensure(blk));
+    uint8_t *d_all = static_cast<uint8_t *>(g_all.ensure(blk * world));
+    merge_pack_block(d_send, d_local, n_send, st);
     KB_NCCL(g_nccl.AllGather(d_send, d_all, blk, NCCL_INT8, g_nccl.comm, st));
-    // 3. concatenate the valid prefixes in rank order, then one stable sort
-    uint64_t off = 0;
-    for (int r = 0; r < world; ++r) {
-        if (counts[r])
-            KB_CUDA(cudaMemcpyAsync(d_cat + off, d_all + (size_t)r * max_c, sizeof(kb_trajectory) * counts[r],
-                                    cudaMemcpyDeviceToDevice, st));
-        off += counts[r];
-    }
-    handle_replace_results(h, d_cat, total, true);
-    uint64_t keep = (top_n && top_n < total) ? top_n : total;
-    handle_replace_results(h, handle_results(h, &n_local), keep, false);
+    // every record places itself in the merged list (results.cu merge_runs_kernel); the list replaces the handle's
+    const uint64_t keep_cap = top_n ? top_n : cap * (uint64_t)world;
+    kb_trajectory *d_out = handle_results_reserve(h, keep_cap);   // may reallocate: the send block is packed already
+    merge_sorted_runs(d_all, blk, world, cap, d_out, keep_cap, d_counts + world + 1, st);
+    uint64_t total = 0;
+    KB_CUDA(cudaMemcpyAsync(&total, d_counts + world + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    KB_CUDA(cudaStreamSynchronize(st));
+    const uint64_t keep = (top_n && top_n < total) ? top_n : total;
+    handle_set_result_count(h, keep);
     if (n_results) *n_results = keep;
     KB_API_END
 }

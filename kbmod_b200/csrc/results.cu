@@ -365,6 +365,79 @@ int sort_trajectories_by_lh(kb_trajectory *d_list, uint64_t n, ResultScratch &sc
     return launches + 1;
 }
 
+// ---- merging the sorted result lists of several GPUs (nccl_merge.cu) --------------------------------------------
+// `blocks` holds `world` blocks of `block_bytes` each: a 32-byte header whose first uint64 is the number of records,
+// then that many 28-byte records sorted by lh descending (the order kb_search leaves).  Every record finds its place
+// in the merged list by itself: its index in its own run, plus the number of records of every earlier run that do
+// not rank behind it, plus the number of records of every later run that rank strictly ahead -- so equal lh values
+// keep (rank, position) order, which is what a stable sort of the concatenation gives (and, with row bands in rank
+// order, the order of a single-GPU search).  One kernel, no passes over the data, nothing to re-sort.
+static constexpr int kMergeHeaderBytes = 32;
+
+__device__ __forceinline__ const kb_trajectory *merge_run(const uint8_t *blocks, size_t block_bytes, int r) {
+    return reinterpret_cast<const kb_trajectory *>(blocks + (size_t)r * block_bytes + kMergeHeaderBytes);
+}
+__device__ __forceinline__ uint64_t merge_count(const uint8_t *blocks, size_t block_bytes, int r) {
+    return *reinterpret_cast<const uint64_t *>(blocks + (size_t)r * block_bytes);
+}
+
+__global__ void merge_runs_kernel(const uint8_t *__restrict__ blocks, size_t block_bytes, int world, uint64_t cap_in,
+                                  kb_trajectory *__restrict__ out, uint64_t keep, uint64_t *total_out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    const uint64_t n_r = min(merge_count(blocks, block_bytes, r), cap_in);
+    if (i == 0 && r == 0 && total_out) {
+        uint64_t tot = 0;
+        for (int q = 0; q < world; ++q) tot += min(merge_count(blocks, block_bytes, q), cap_in);
+        *total_out = tot;
+    }
+    if (i >= n_r) return;
+    const kb_trajectory me = merge_run(blocks, block_bytes, r)[i];
+    const uint32_t key = lh_key(me.lh);
+    uint64_t pos = i;
+    for (int q = 0; q < world; ++q) {
+        if (q == r) continue;
+        const kb_trajectory *run = merge_run(blocks, block_bytes, q);
+        const uint64_t n_q = min(merge_count(blocks, block_bytes, q), cap_in);
+        // earlier run: count keys <= mine; later run: count keys < mine (keys ascend along a run)
+        uint64_t lo = 0, hi = n_q;
+        while (lo < hi) {
+            const uint64_t mid = (lo + hi) >> 1;
+            const uint32_t k = lh_key(run[mid].lh);
+            const bool before = (q < r) ? (k <= key) : (k < key);
+            if (before) lo = mid + 1;
+            else hi = mid;
+        }
+        pos += lo;
+    }
+    if (pos < keep) out[pos] = me;
+}
+
+__global__ void merge_header_kernel(uint8_t *block, uint64_t n) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *reinterpret_cast<uint64_t *>(block) = n;
+}
+
+int merge_header_bytes() { return kMergeHeaderBytes; }
+
+int merge_pack_block(void *d_block, const kb_trajectory *d_list, uint64_t n, cudaStream_t st) {
+    merge_header_kernel<<<1, 32, 0, st>>>(static_cast<uint8_t *>(d_block), n);
+    if (n)
+        KB_CUDA(cudaMemcpyAsync(static_cast<uint8_t *>(d_block) + kMergeHeaderBytes, d_list, sizeof(kb_trajectory) * n,
+                                cudaMemcpyDeviceToDevice, st));
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int merge_sorted_runs(const void *d_blocks, size_t block_bytes, int world, uint64_t cap_in, kb_trajectory *d_out,
+                      uint64_t keep, uint64_t *d_total, cudaStream_t st) {
+    if (cap_in == 0) cap_in = 1;  // the grid still has to run once for the total
+    dim3 grid((unsigned)((cap_in + 255) / 256), (unsigned)world);
+    merge_runs_kernel<<<grid, 256, 0, st>>>(static_cast<const uint8_t *>(d_blocks), block_bytes, world, cap_in, d_out, keep,
+                                            d_total);
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
 // ---- merging deferred sigma-G survivors into the per-pixel slots ------------------------------------------------
 __global__ void surv_keys_kernel(const ClipSurvivor *__restrict__ surv, uint64_t n, uint32_t *keys, uint32_t *vals) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

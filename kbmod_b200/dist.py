@@ -49,6 +49,21 @@ def merge_sorted_lists(lists, top_n=0):
     return out[:top_n] if top_n else out
 
 
+def merge_sorted_lists_device(lists, top_n=0):
+    """The same merge on the device (``kb_merge_sorted_lists``: the kernel the NCCL merge runs on the gathered
+    blocks), from host arrays."""
+    from ._lib import ptr, ptr_array
+    arrs = [np.ascontiguousarray(a, dtype=TRAJECTORY_DTYPE) for a in lists]
+    counts = np.array([a.size for a in arrs], dtype=np.uint64)
+    total = int(counts.sum())
+    keep = min(total, top_n) if top_n else total
+    out = np.zeros(max(keep, 1), dtype=TRAJECTORY_DTYPE)
+    n = C.c_uint64(0)
+    check(lib.kb_merge_sorted_lists(ptr_array(arrs), ptr(counts), C.c_int(len(arrs)), C.c_uint64(top_n), ptr(out),
+                                    C.byref(n)))
+    return out[: n.value]
+
+
 class Comm:
     """Control-plane communicator (gloo) + the library's NCCL communicator for the data path."""
 
