@@ -61,7 +61,7 @@ typedef struct {
     uint64_t evals;        /* start pixels * candidates * times of that search */
     uint32_t search_launches; /* number of search-kernel launches */
     uint32_t total_launches;  /* all kernels launched by the call */
-    uint32_t used_tiled;      /* 1 when the TMA-staged tiled kernel ran, 0 for the generic kernel */
+    uint32_t used_tiled;      /* 1 when the TMA-staged tiled kernel ran, 2 the candidate-parallel one, 0 the generic one */
     float ms_main_kernel;     /* the single gather kernel launch alone (search_tiled_kernel / search_generic_kernel) */
     uint64_t h2d_stack_bytes; /* psi/phi bytes copied host -> device inside the call (0 when the stack was resident) */
 } kb_timing;
@@ -137,8 +137,13 @@ KB_EXPORT int kb_get_timing(kb_handle h, kb_timing *t);
 /* The raw K*P per-pixel slots of the last search in the reference's order ((y_i*sw + x_i)*K + r), i.e. what
  * searchFilterImages leaves in `results` before the host filter (kernels.cu:285-301,322-330). Debug/tests. */
 KB_EXPORT int kb_get_slots(kb_handle h, kb_trajectory *out, uint64_t capacity, uint64_t *n_slots);
-/* 0 = choose automatically, 1 = force the generic kernel, 2 = force the tiled TMA kernel (error if unusable). */
+/* 0 = choose automatically, 1 = force the generic kernel, 2 = force the tiled TMA kernel (error if unusable),
+ * 3 = force the candidate-parallel kernel (small start windows with long per-pixel lists, as TrajectoryExplorer
+ * drives StackSearch: trajectory_explorer.py:221-255). */
 KB_EXPORT int kb_set_kernel_mode(kb_handle h, int mode);
+/* Why the last kb_search on this handle did not run on the tiled kernel ("" when it did): borrowed string, valid
+ * until the next search.  The Python layer logs it (the reference has one kernel and nothing to report). */
+KB_EXPORT int kb_search_note(kb_handle h, const char **note);
 
 /* StackSearch::evaluate_single_trajectory(trj, use_kernel=true) (stack_search.cpp:193-209 -> evaluateTrajectory
  * kernels.cu:154-242): fills lh, flux, obs_count of each trajectory in place, on the device.  keep_mask
@@ -175,6 +180,14 @@ KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64
                                       uint8_t *obs_valid_io, int has_obs_valid, double *lh_out, double *flux_out,
                                       int64_t *obs_count_out);
 
+/* SigmaGClipping.compute_clipped_sigma_g (filters/sigma_g_filter.py:86-112): one float64 likelihood curve of n points.
+ * Percentiles as numpy.percentile computes them (method "linear", float64) over all points, or over the positive
+ * ones when clip_negative != 0 (none positive: nothing is kept); kept are the points strictly inside
+ * median -/+ n_sigma * coeff * max(upper - lower, 1e-8).  good_idx (room for n entries) receives their indices in
+ * ascending order, *n_good their number.  Host pointers; n <= 65536. */
+KB_EXPORT int kb_sigmag_clip_curve(const double *lh, uint32_t n, double low_pct, double high_pct, double n_sigma,
+                                   double coeff, int clip_negative, int64_t *good_idx, uint32_t *n_good);
+
 /* TrajectoryClusterGrid / apply_trajectory_grid_filter (filters/clustering_grid.py:13-176): every trajectory falls
  * into the spatial bin (int(x/w), int(y/w), int((x + max_time*vx)/w), int((y + max_time*vy)/w)); idx_out receives,
  * for every occupied bin in the order the bins are first seen, the index of its best trajectory (largest lh; the
@@ -201,6 +214,12 @@ KB_EXPORT int kb_coadd_stamps(const float *const *sci, const float *const *var, 
 KB_EXPORT int kb_extract_stamps(const float *const *sci, int T, int H, int W, const double *times, const double *x0,
                                 const double *y0, const double *vx, const double *vy, uint64_t n, int radius,
                                 float *out);
+
+/* extract_curve_values (core/stamp_utils.py:87-141): out[r][t] = imgs[t][y_vals[r][t]][x_vals[r][t]] as float64 where
+ * that pixel exists, NaN elsewhere.  x_vals / y_vals / out are n x T, row-major; imgs are T pointers to H x W float32
+ * images (any stack: science, variance, psi, phi).  Host pointers. */
+KB_EXPORT int kb_extract_curve_values(const float *const *imgs, int T, int H, int W, const int64_t *x_vals,
+                                      const int64_t *y_vals, uint64_t n, double *out);
 
 /* ---- measurement hooks (no reference counterpart) ---------------------------------------------------- */
 /* CUDA events recorded on the handle's own stream, so a caller can time a region of calls on the device:

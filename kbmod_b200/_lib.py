@@ -52,9 +52,9 @@ SYMBOLS = [
     "kb_create_from_images", "kb_create_from_images_rows", "kb_create_from_psi_phi", "kb_destroy", "kb_get_meta", "kb_host_array",
     "kb_read_psi_phi", "kb_read_time", "kb_preload", "kb_unload", "kb_on_gpu", "kb_search", "kb_get_results",
     "kb_num_results", "kb_set_results", "kb_clear_results", "kb_get_timing", "kb_get_slots",
-    "kb_set_kernel_mode", "kb_evaluate_trajectories", "kb_psi_phi_curves", "kb_sigmag_filtered_indices",
+    "kb_set_kernel_mode", "kb_search_note", "kb_evaluate_trajectories", "kb_psi_phi_curves", "kb_sigmag_filtered_indices",
     "kb_timer_start", "kb_timer_stop", "kb_measure_peaks", "kb_sort_trajectories_static", "kb_nccl_unique_id", "kb_nccl_init", "kb_nccl_finalize", "kb_merge_results_allgather", "kb_merge_sorted_lists",
-    "kb_sigmag_clip_matrix", "kb_update_likelihood", "kb_sigmag_filter_curves", "kb_coadd_stamps", "kb_grid_filter", "kb_extract_stamps",
+    "kb_sigmag_clip_matrix", "kb_sigmag_clip_curve", "kb_extract_curve_values", "kb_update_likelihood", "kb_sigmag_filter_curves", "kb_coadd_stamps", "kb_grid_filter", "kb_extract_stamps",
 ]
 
 if not os.path.exists(LIB_PATH):

@@ -89,7 +89,8 @@ struct kb_stack_s {
     int kernel_mode = 0;
     // search state
     DevBuf<float> d_vx, d_vy;
-    DevBuf<Slot> d_slots;
+    DevBuf<Slot> d_slots, d_pairs;
+    std::string search_note;   // why the last search did not run on the tiled kernel (empty when it did)
     uint64_t n_slots = 0;
     kb_params last_params{};
     bool have_slots = false;
@@ -937,9 +938,15 @@ int kb_on_gpu(kb_handle h, int *flag) {
     KB_API_END
 }
 
+int kb_search_note(kb_handle h, const char **note) {
+    KB_API_BEGIN
+    *note = h->search_note.c_str();
+    KB_API_END
+}
+
 int kb_set_kernel_mode(kb_handle h, int mode) {
     KB_API_BEGIN
-    if (mode < 0 || mode > 2) throw Error("kernel mode must be 0, 1 or 2");
+    if (mode < 0 || mode > 3) throw Error("kernel mode must be 0, 1, 2 or 3");
     h->kernel_mode = mode;
     KB_API_END
 }
@@ -1028,13 +1035,38 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     }
     h->d_slots.ensure(n_slots);
     const StackView sv = make_view(h);
+    // Which kernel: the tiled one when it can take the search (results_per_pixel <= 8, ...); the candidate-parallel
+    // one for longer per-pixel lists over few start pixels; the generic one for everything else.  Whenever the tiled
+    // kernel is not the one that runs, the reason is kept for the caller (kb_search_note; the Python layer logs it).
     TiledPlan *plan = nullptr;
     std::string why;
-    if (h->kernel_mode != 1) {
+    bool use_pairs = false;
+    h->search_note.clear();
+    if (h->kernel_mode == 0 || h->kernel_mode == 2) {
         plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data());
         if (!plan && h->kernel_mode == 2) throw Error("tiled kernel not usable: " + why);
-        if (!plan && getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] generic kernel used: %s\n", why.c_str());
+    } else {
+        why = h->kernel_mode == 1 ? "generic kernel requested" : "candidate-parallel kernel requested";
     }
+    // automatic mode, a start window of a few tiles only (the tiled kernel gives every tile to one SM): spread the
+    // (pixel, candidate) pairs over the device instead
+    const uint64_t n_tiles = ((sw + 63) / 64) * ((sh + 14) / 15);
+    if (plan && h->kernel_mode == 0 && n_tiles < 37 && search_pairs_usable(p, n_cand, nullptr)) {
+        tiled_plan_destroy(plan);
+        plan = nullptr;
+        why = "the start window covers only " + std::to_string(n_tiles) + " tiles of the tiled kernel";
+    }
+    if (!plan && (h->kernel_mode == 3 || (h->kernel_mode == 0 && (p.results_per_pixel > (uint32_t)kMaxRegK || n_tiles < 37)))) {
+        std::string why_pairs;
+        use_pairs = search_pairs_usable(p, n_cand, &why_pairs);
+        if (!use_pairs && h->kernel_mode == 3) throw Error("candidate-parallel kernel not usable: " + why_pairs);
+        if (!use_pairs) why += "; " + why_pairs;
+    }
+    if (!plan) {
+        h->search_note = std::string(use_pairs ? "candidate-parallel kernel used: " : "generic kernel used: ") + why;
+        if (getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] %s\n", h->search_note.c_str());
+    }
+    if (use_pairs) h->d_pairs.ensure(sw * sh * n_cand);
     t_prep.stop(st);
 
     t_search.start(st);
@@ -1045,6 +1077,8 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
         if (plan)
             sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st,
                                      pipelined ? &h->up : nullptr);
+        else if (use_pairs)
+            sl = launch_search_pairs(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, h->d_pairs.p, h->scratch, st);
         else sl = launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
     } catch (...) {
         if (plan) tiled_plan_destroy(plan);
@@ -1053,7 +1087,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_search.stop(st);
     launches += sl;
     h->timing.search_launches = sl;
-    h->timing.used_tiled = plan ? 1 : 0;
+    h->timing.used_tiled = plan ? 1 : (use_pairs ? 2 : 0);
 
     t_post.start(st);
     uint64_t n_keep = 0;

@@ -175,6 +175,13 @@ struct ResultScratch {
     uint32_t *d_flag = nullptr;   // invalid-trajectory flag
 };
 void result_scratch_free(ResultScratch &s);
+void result_scratch_reserve(ResultScratch &s, uint64_t items);   // room for `items` key/index pairs
+int radix_sort_u32_pairs(ResultScratch &scr, uint64_t n, cudaStream_t st);  // scr.keys[0]/vals[0], stable, ascending
+// search_pairs.cu: candidate-parallel search (one thread per (start pixel, candidate) pair + two stable sorts)
+static constexpr uint64_t kMaxSearchPairs = 1ull << 27;
+bool search_pairs_usable(const kb_params &p, uint64_t n_cand, std::string *why_not);
+int launch_search_pairs(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, uint64_t n_cand,
+                        Slot *d_slots, Slot *d_pairs, ResultScratch &scr, cudaStream_t st);
 // clustering_grid.py: indices of the best trajectory of every spatial bin, bins in first-seen order.
 int grid_filter_indices(const kb_trajectory *d_list, uint64_t n, double bin_width, double max_time,
                         uint32_t *d_idx_out, uint64_t *n_out, ResultScratch &scr, cudaStream_t st);

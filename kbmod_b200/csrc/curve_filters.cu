@@ -13,6 +13,10 @@
 //   * the sums of _update_likelihood follow numpy's float32 pairwise summation (blocks of 128, 8 partial sums).
 #include <math.h>
 
+#include <math_constants.h>
+
+#include <vector>
+
 #include "common.cuh"
 
 namespace kb {
@@ -174,6 +178,67 @@ void check_shape(uint64_t R, unsigned T) {
     if (R * (uint64_t)T >= (1ull << 40)) throw Error("curve matrix too large");
 }
 
+// One curve, one CTA: rank the selected values by counting (ties in index order), scatter them into sorted order,
+// then thread 0 takes numpy's three percentiles and every thread tests its own points.
+__device__ __forceinline__ double np_lerp(double a, double b, double t) {   // numpy/lib/function_base.py _lerp
+    const double d = __dsub_rn(b, a);
+    return (t >= 0.5) ? __dsub_rn(b, __dmul_rn(d, __dsub_rn(1.0, t))) : __dadd_rn(a, __dmul_rn(d, t));
+}
+__device__ __forceinline__ double np_percentile_sorted(const double *v, unsigned m, double pct) {
+    const double q = pct / 100.0;
+    const double virt = __dmul_rn((double)(m - 1), q);
+    if (virt >= (double)(m - 1)) return v[m - 1];
+    const double fl = floor(virt);
+    const unsigned lo = (unsigned)fl;
+    return np_lerp(v[lo], v[lo + 1], __dsub_rn(virt, fl));
+}
+__global__ void __launch_bounds__(1024)
+        sigmag_curve_kernel(const double *__restrict__ lh, unsigned n, double low_pct, double high_pct, double n_sigma,
+                            double coeff, int clip_negative, double *__restrict__ sorted, uint8_t *__restrict__ flags) {
+    __shared__ unsigned s_m;
+    __shared__ int s_nan;
+    __shared__ double s_lo, s_hi;
+    if (threadIdx.x == 0) {
+        s_m = 0;
+        s_nan = 0;
+    }
+    __syncthreads();
+    // selected = all points, or the positive ones (clip_negative); rank by counting among the selected
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+        const double vi = lh[i];
+        const bool sel = clip_negative ? (vi > 0.0) : true;
+        if (!sel) continue;
+        if (vi != vi) s_nan = 1;   // numpy's percentile of data with a NaN is NaN: nothing passes
+        unsigned rank = 0;
+        for (unsigned j = 0; j < n; ++j) {
+            const double vj = lh[j];
+            const bool selj = clip_negative ? (vj > 0.0) : true;
+            if (selj && (vj < vi || (vj == vi && j < i))) ++rank;
+        }
+        sorted[rank] = vi;
+        atomicAdd(&s_m, 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned m = s_m;
+        if (m == 0 || s_nan) {
+            s_lo = CUDART_NAN;
+            s_hi = CUDART_NAN;
+        } else {
+            const double lower = np_percentile_sorted(sorted, m, low_pct);
+            const double median = np_percentile_sorted(sorted, m, 50.0);
+            const double upper = np_percentile_sorted(sorted, m, high_pct);
+            const double delta = fmax(__dsub_rn(upper, lower), 1e-8);
+            const double ns = __dmul_rn(n_sigma, __dmul_rn(coeff, delta));
+            s_lo = __dsub_rn(median, ns);
+            s_hi = __dadd_rn(median, ns);
+        }
+    }
+    __syncthreads();
+    const double lo = s_lo, hi = s_hi;
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) flags[i] = (lh[i] > lo && lh[i] < hi) ? 1 : 0;
+}
+
 void launch_clip(const float *d_lh, const float *d_psi, const float *d_phi, const uint8_t *d_obs, uint64_t R,
                  unsigned T, float q_low, float q_high, float mult, int clip_negative, uint8_t *d_valid) {
     const size_t smem = sizeof(float) * (size_t)T * kCurveWarps;
@@ -252,6 +317,36 @@ KB_EXPORT int kb_sigmag_filter_curves(const float *psi, const float *phi, uint64
     KB_CUDA(cudaMemcpy(lh_out, d_lh.p, n_rows * 8, cudaMemcpyDeviceToHost));
     KB_CUDA(cudaMemcpy(flux_out, d_flux.p, n_rows * 8, cudaMemcpyDeviceToHost));
     KB_CUDA(cudaMemcpy(obs_count_out, d_cnt.p, n_rows * 8, cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
+
+// SigmaGClipping.compute_clipped_sigma_g (filters/sigma_g_filter.py:86-112): ONE likelihood curve, float64, numpy's
+// percentile (method "linear": virtual index q/100 * (n - 1), value = lerp of the two neighbours, taken from the
+// nearer end exactly as numpy's _lerp does), delta floored at 1e-8, strict bounds on the whole curve.  good_idx (room
+// for n entries) receives the indices kept, in ascending order.
+KB_EXPORT int kb_sigmag_clip_curve(const double *lh, uint32_t n, double low_pct, double high_pct, double n_sigma,
+                                   double coeff, int clip_negative, int64_t *good_idx, uint32_t *n_good) {
+    KB_API_BEGIN
+    if (!n_good) throw Error("null argument");
+    *n_good = 0;
+    if (n == 0) return 0;
+    if (!lh || !good_idx) throw Error("null argument");
+    if (n > 65536) throw Error("likelihood curve too long (at most 65536 points)");
+    int dev_count = 0;
+    if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0)
+        throw Error("no CUDA device: kbmod_b200 has no CPU path");
+    DevBuf d_lh((size_t)n * 8), d_sorted((size_t)n * 8), d_flags(n), d_cnt(4);
+    KB_CUDA(cudaMemcpy(d_lh.p, lh, (size_t)n * 8, cudaMemcpyHostToDevice));
+    sigmag_curve_kernel<<<1, 1024>>>(d_lh.as<double>(), n, low_pct, high_pct, n_sigma, coeff, clip_negative,
+                                     d_sorted.as<double>(), d_flags.as<uint8_t>());
+    KB_CUDA(cudaGetLastError());
+    std::vector<uint8_t> flags(n);
+    KB_CUDA(cudaMemcpy(flags.data(), d_flags.p, n, cudaMemcpyDeviceToHost));
+    uint32_t k = 0;
+    for (uint32_t i = 0; i < n; ++i)
+        if (flags[i]) good_idx[k++] = (int64_t)i;
+    *n_good = k;
     KB_API_END
 }
 

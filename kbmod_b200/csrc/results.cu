@@ -277,6 +277,9 @@ static void ensure_scratch(ResultScratch &s, uint64_t items, uint64_t cblocks) {
     }
 }
 
+void result_scratch_reserve(ResultScratch &s, uint64_t items) { ensure_scratch(s, items, 1); }
+int radix_sort_u32_pairs(ResultScratch &scr, uint64_t n, cudaStream_t st) { return radix_sort_pairs(scr, n, st); }
+
 void result_scratch_free(ResultScratch &s) {
     for (int i = 0; i < 2; ++i) {
         if (s.keys[i]) cudaFree(s.keys[i]);

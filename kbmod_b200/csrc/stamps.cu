@@ -11,6 +11,7 @@
 // final value is narrowed to float32 -- bit-identical to the reference.  The median is torch.nanmedian's: the lower of
 // the two middle values for an even count.  Pixels with no data at any time give 0 in every coadd.
 #include <math.h>
+#include <math_constants.h>
 
 #include "common.cuh"
 
@@ -234,5 +235,42 @@ extern "C" KB_EXPORT int kb_extract_stamps(const float *const *sci, int T, int H
                                      n, radius, d_out.as<float>());
     KB_CUDA(cudaGetLastError());
     KB_CUDA(cudaMemcpy(out, d_out.p, total * 4, cudaMemcpyDeviceToHost));
+    KB_API_END
+}
+
+// extract_curve_values (core/stamp_utils.py:87-141 over _extract_curve_values, :477-512): values[r][t] =
+// imgs[t][y[r][t]][x[r][t]] where that pixel exists, NaN elsewhere; float64 like the reference's np.full(..., nan).
+namespace kb {
+__global__ void curve_values_kernel(const float *__restrict__ img, int H, int W, const int64_t *__restrict__ x,
+                                    const int64_t *__restrict__ y, uint64_t R, int T, int t, double *__restrict__ out) {
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    const int64_t xi = x[r * T + t], yi = y[r * T + t];
+    double v = CUDART_NAN;
+    if (xi >= 0 && xi < W && yi >= 0 && yi < H) v = (double)img[(size_t)yi * W + (size_t)xi];
+    out[r * T + t] = v;
+}
+}  // namespace kb
+
+extern "C" KB_EXPORT int kb_extract_curve_values(const float *const *imgs, int T, int H, int W, const int64_t *x_vals,
+                                                 const int64_t *y_vals, uint64_t n, double *out) {
+    KB_API_BEGIN
+    int dev_count = 0;
+    if (cudaGetDeviceCount(&dev_count) != cudaSuccess || dev_count == 0)
+        throw Error("no CUDA device: kbmod_b200 has no CPU path");
+    if (T <= 0 || H <= 0 || W <= 0) throw Error("empty image stack");
+    if (n == 0) return 0;
+    if (!imgs || !x_vals || !y_vals || !out) throw Error("null argument");
+    const size_t img = (size_t)H * W, cells = (size_t)n * T;
+    DBuf d_img[2] = {DBuf(img * 4), DBuf(img * 4)}, d_x(cells * 8), d_y(cells * 8), d_out(cells * 8);
+    KB_CUDA(cudaMemcpy(d_x.p, x_vals, cells * 8, cudaMemcpyHostToDevice));
+    KB_CUDA(cudaMemcpy(d_y.p, y_vals, cells * 8, cudaMemcpyHostToDevice));
+    for (int t = 0; t < T; ++t) {   // one image at a time: nothing but the current image has to be on the device
+        KB_CUDA(cudaMemcpy(d_img[t & 1].p, imgs[t], img * 4, cudaMemcpyHostToDevice));
+        kb::curve_values_kernel<<<(unsigned)((n + 255) / 256), 256>>>(d_img[t & 1].as<float>(), H, W, d_x.as<int64_t>(),
+                                                                      d_y.as<int64_t>(), n, T, t, d_out.as<double>());
+    }
+    KB_CUDA(cudaGetLastError());
+    KB_CUDA(cudaMemcpy(out, d_out.p, cells * 8, cudaMemcpyDeviceToHost));
     KB_API_END
 }

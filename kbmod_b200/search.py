@@ -642,7 +642,8 @@ class StackSearch:
         return self._ppa.on_gpu
 
     def set_kernel_mode(self, mode):
-        """0 = automatic, 1 = generic kernel, 2 = tiled TMA kernel (extension; used by the parity tests)."""
+        """0 = automatic, 1 = generic kernel, 2 = tiled TMA kernel, 3 = candidate-parallel kernel (extension; used by
+        the parity tests)."""
         check(lib.kb_set_kernel_mode(self._ppa._require(), C.c_int(mode)))
 
     # -- search -------------------------------------------------------------------------------------
@@ -677,6 +678,10 @@ class StackSearch:
         cp = p._c()
         self._result_cache = None
         check(lib.kb_search(self._ppa._require(), C.byref(cp), ptr(vx), ptr(vy), C.c_uint64(vx.size), C.byref(n)))
+        note = C.c_char_p()
+        check(lib.kb_search_note(self._ppa._require(), C.byref(note)))
+        if note.value:   # the search ran, but not on the throughput kernel: say why
+            self._log.warning("kbmod_b200: " + note.value.decode("utf-8", "replace"))
         self._log.debug(f"Core search returned {n.value} results after filtering by LH and min_obs.")
         timer.stop()
 

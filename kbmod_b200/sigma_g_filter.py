@@ -77,9 +77,20 @@ class SigmaGClipping:
         return out.astype(bool)
 
     def compute_clipped_sigma_g(self, lh):
-        """Single curve (sigma_g_filter.py:86-112).  The reference evaluates this one with numpy's float64
-        percentile and a 1e-8 floor -- different arithmetic from the matrix form -- on the CPU only."""
-        raise RuntimeError("kbmod_b200 has no CPU path; use compute_clipped_sigma_g_matrix(lh[None, :]).")
+        """Single likelihood curve -> indices that pass (sigma_g_filter.py:86-112): numpy's float64 percentiles and a
+        1e-8 floor -- different arithmetic from the matrix form -- evaluated on the device (kb_sigmag_clip_curve)."""
+        require_gpu()
+        lh = np.ascontiguousarray(lh, dtype=np.float64)
+        if lh.ndim != 1:
+            raise ValueError("lh must be a single likelihood curve")
+        if lh.size == 0 or (self.clip_negative and np.count_nonzero(lh > 0) == 0):
+            return np.array([]) if lh.size and self.clip_negative else np.array([], dtype=np.int64)
+        idx = np.zeros(lh.size, dtype=np.int64)
+        n = C.c_uint32(0)
+        check(lib.kb_sigmag_clip_curve(ptr(lh), C.c_uint32(lh.size), C.c_double(self.low_bnd), C.c_double(self.high_bnd),
+                                       C.c_double(self.n_sigma), C.c_double(self.coeff),
+                                       C.c_int(1 if self.clip_negative else 0), ptr(idx), C.byref(n)))
+        return idx[: n.value]
 
 
 def update_likelihood(psi, phi, obs_valid=None):

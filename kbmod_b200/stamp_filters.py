@@ -85,6 +85,33 @@ def extract_all_stamps(sci, zeroed_times, x, y, vx, vy, radius):
     return out
 
 
+def extract_curve_values(imgs, x_vals, y_vals):
+    """core/stamp_utils.py:87-141: the values of a stack of T images (a T x H x W array or a list of H x W arrays) at
+    predicted integer positions -- a length-T array for one trajectory, R x T for R of them; NaN off the image."""
+    imgs = [f32(a) for a in imgs]
+    num_times = len(imgs)
+    x_vals = np.asanyarray(x_vals, dtype=int)
+    if x_vals.ndim == 1:
+        x_vals = x_vals[np.newaxis, :]
+    if x_vals.shape[1] != num_times:
+        raise ValueError(f"X values must have the same length as times ({num_times}).")
+    y_vals = np.asanyarray(y_vals, dtype=int)
+    if y_vals.ndim == 1:
+        y_vals = y_vals[np.newaxis, :]
+    if y_vals.shape[1] != num_times:
+        raise ValueError(f"Y values must have the same length as times ({num_times}).")
+    if x_vals.shape[0] != y_vals.shape[0]:
+        raise ValueError("X and Y values must have the same number of results.")
+    require_gpu()
+    H, W = imgs[0].shape
+    xv, yv = np.ascontiguousarray(x_vals, dtype=np.int64), np.ascontiguousarray(y_vals, dtype=np.int64)
+    out = np.full(xv.shape, np.nan)
+    if xv.size:
+        check(lib.kb_extract_curve_values(ptr_array(imgs), C.c_int(num_times), C.c_int(H), C.c_int(W), ptr(xv), ptr(yv),
+                                          C.c_uint64(xv.shape[0]), ptr(out)))
+    return out.flatten() if x_vals.shape[0] == 1 else out
+
+
 def append_all_stamps(result_data, im_stack, stamp_radius):
     """filters/stamp_filters.py:163-211: the ``all_stamps`` column (R x T x S x S float32)."""
     if stamp_radius < 1:

@@ -253,3 +253,40 @@ def grid_filter_indices(x, y, vx, vy, lh, bin_width, max_time, vectorised=False)
         elif float(lh[i]) > float(lh[table[key]]):
             table[key] = i
     return np.array([table[k] for k in order], dtype=np.int64)
+
+
+# ---- single-curve sigma-G clip (filters/sigma_g_filter.py:86-112) ------------------------------------------------------
+def _np_percentile_sorted(v, pct):
+    """numpy.percentile, method 'linear', on an ascending float64 array, spelled out: virtual index (n - 1) * q,
+    the two neighbours, and numpy's _lerp (from the nearer end)."""
+    m = len(v)
+    virt = (m - 1) * (pct / 100.0)
+    if virt >= m - 1:
+        return v[m - 1]
+    lo = int(np.floor(virt))
+    t = virt - np.floor(virt)
+    d = v[lo + 1] - v[lo]
+    return v[lo + 1] - d * (1 - t) if t >= 0.5 else v[lo] + d * t
+
+
+def sigmag_clip_curve(lh, low_bnd, high_bnd, n_sigma, coeff, clip_negative):
+    """Indices kept by SigmaGClipping.compute_clipped_sigma_g for one float64 likelihood curve."""
+    lh = np.asarray(lh, dtype=np.float64)
+    sel = lh[lh > 0] if clip_negative else lh
+    if len(sel) == 0 or np.isnan(sel).any():
+        return np.zeros(0, dtype=np.int64)
+    v = np.sort(sel, kind="stable")
+    lower, median, upper = (_np_percentile_sorted(v, q) for q in (low_bnd, 50, high_bnd))
+    n_sigma_g = n_sigma * (coeff * max(upper - lower, 1e-8))
+    return np.where(np.logical_and(lh > median - n_sigma_g, lh < median + n_sigma_g))[0].astype(np.int64)
+
+
+def extract_curve_values(imgs, x_vals, y_vals):
+    """core/stamp_utils.py:477-512 (_extract_curve_values): R x T float64, NaN off the image."""
+    x_vals, y_vals = np.atleast_2d(np.asarray(x_vals, dtype=int)), np.atleast_2d(np.asarray(y_vals, dtype=int))
+    out = np.full(x_vals.shape, np.nan)
+    for t, img in enumerate(imgs):
+        h, w = img.shape
+        ok = (x_vals[:, t] >= 0) & (x_vals[:, t] < w) & (y_vals[:, t] >= 0) & (y_vals[:, t] < h)
+        out[ok, t] = img[y_vals[ok, t], x_vals[ok, t]]
+    return out

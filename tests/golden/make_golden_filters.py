@@ -97,6 +97,18 @@ def main():
             out[f"c{i}_lh_curves"], out[f"c{i}_valid"] = lh, valid
             out[f"c{i}_coeff"] = np.float64(clipper.coeff)
             out[f"c{i}_lh"], out[f"c{i}_flux"], out[f"c{i}_obs"] = ulh, uflux, uobs.astype(np.int64)
+        # single curves through compute_clipped_sigma_g (numpy float64 percentiles): rows of the first cases, as float64
+        singles = []
+        for i in (0, 2, 4):
+            R, T, lo, hi, ns, neg = cases[i]
+            lh = np.nan_to_num(out[f"c{i}_lh_curves"].astype(np.float64), nan=0.0)
+            for neg_flag in (False, True):
+                clipper = ref.SigmaGClipping(lo, hi, ns, neg_flag)
+                for r in range(min(int(R), 8)):
+                    singles.append((i, r, neg_flag, np.asarray(clipper.compute_clipped_sigma_g(lh[r]), dtype=np.int64)))
+        out["single_meta"] = np.array([(a, b, int(c)) for a, b, c, _ in singles], dtype=np.int64)
+        for k, (_, _, _, idx) in enumerate(singles):
+            out[f"single_{k}"] = idx
     np.savez_compressed(os.path.join(HERE, "sigmag_filter_case.npz"), **out)
     print("wrote sigmag_filter_case.npz:", {k: v.shape for k, v in out.items() if k.endswith("_valid")})
 

@@ -79,6 +79,8 @@ def main():
         for k, a in co.items():
             out[f"{tag}_{k}"] = a
     out["all_stamps_r2"] = np.asanyarray(su.extract_stamp_stack(sci, xvals[2], yvals[2], radius)).astype(np.float32)
+    out["curve_values"] = np.asarray(su.extract_curve_values(sci, xvals, yvals), dtype=np.float64)     # R x T
+    out["curve_values_one"] = np.asarray(su.extract_curve_values(sci, xvals[2], yvals[2]), dtype=np.float64)
     np.savez_compressed(os.path.join(HERE, "stamps_case.npz"), **out)
     print("wrote stamps_case.npz")
 

@@ -45,6 +45,21 @@ def test_oracle_matches_reference_fixtures(golden):
         assert np.array_equal(uobs, golden[f"c{i}_obs"])
 
 
+def _single_cases(golden):
+    for k, (i, r, neg) in enumerate(golden["single_meta"]):
+        R, T, lo, hi, ns, _ = golden["cases"][i]
+        lh = np.nan_to_num(golden[f"c{i}_lh_curves"].astype(np.float64), nan=0.0)[r]
+        yield k, lh, float(lo), float(hi), float(ns), bool(neg), float(golden[f"c{i}_coeff"])
+
+
+def test_oracle_single_curve_clip_matches_reference_fixtures(golden):
+    n = 0
+    for k, lh, lo, hi, ns, neg, coeff in _single_cases(golden):
+        assert np.array_equal(of.sigmag_clip_curve(lh, lo, hi, ns, coeff, neg), golden[f"single_{k}"]), k
+        n += len(golden[f"single_{k}"])
+    assert n > 100
+
+
 def test_oracle_pairwise_sum_is_numpys():
     rng = np.random.default_rng(5)
     for n in [0, 1, 7, 8, 9, 64, 127, 128, 129, 255, 256, 257, 400, 1000, 4096]:
@@ -89,6 +104,22 @@ def test_gpu_clip_matrix_bit_exact(golden):
         got = SigmaGClipping(lo, hi, ns, neg).compute_clipped_sigma_g_matrix(golden[f"c{i}_lh_curves"])
         assert got.dtype == bool and got.shape == (R, T)
         assert np.array_equal(got, golden[f"c{i}_valid"]), f"case {i}"
+
+
+@pytest.mark.gpu
+def test_gpu_single_curve_clip_matches_reference_fixtures(golden):
+    """SigmaGClipping.compute_clipped_sigma_g (sigma_g_filter.py:86-112; float64, numpy percentiles) on the device."""
+    from kbmod_b200.sigma_g_filter import SigmaGClipping
+    for k, lh, lo, hi, ns, neg, _ in _single_cases(golden):
+        got = SigmaGClipping(lo, hi, ns, neg).compute_clipped_sigma_g(lh)
+        assert np.array_equal(got, golden[f"single_{k}"]), k
+    rng = np.random.default_rng(3)
+    for n in (1, 2, 3, 50, 1025, 5000):
+        lh = np.round(rng.normal(2, 3, n), 2)     # ties
+        for neg in (False, True):
+            c = SigmaGClipping(20, 80, 2.5, neg)
+            assert np.array_equal(c.compute_clipped_sigma_g(lh), of.sigmag_clip_curve(lh, 20, 80, 2.5, c.coeff, neg)), (n, neg)
+    assert len(SigmaGClipping(25, 75, 2, True).compute_clipped_sigma_g(np.array([-1.0, -2.0, 0.0]))) == 0
 
 
 @pytest.mark.gpu

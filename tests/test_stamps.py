@@ -35,6 +35,30 @@ def test_oracle_matches_reference_fixtures(golden):
     assert same_f32(st.astype(np.float32), g["all_stamps_r2"])
 
 
+def test_oracle_curve_values_match_reference_fixture(golden):
+    g = golden
+    xs = of.stamp_positions(g["times"], g["x"], g["vx"])
+    ys = of.stamp_positions(g["times"], g["y"], g["vy"])
+    got = of.extract_curve_values(list(g["sci"]), xs, ys)
+    assert got.dtype == np.float64 and np.array_equal(got, g["curve_values"], equal_nan=True)
+    assert np.isnan(got).any() and np.isfinite(got).any()
+
+
+@pytest.mark.gpu
+def test_gpu_extract_curve_values_matches_reference_fixture(golden):
+    """extract_curve_values (core/stamp_utils.py:87-141) on the device: R x T float64, NaN off the image."""
+    from kbmod_b200.stamp_filters import extract_curve_values
+    g = golden
+    xs = of.stamp_positions(g["times"], g["x"], g["vx"])
+    ys = of.stamp_positions(g["times"], g["y"], g["vy"])
+    got = extract_curve_values(g["sci"], xs, ys)
+    assert got.dtype == np.float64 and np.array_equal(got, g["curve_values"], equal_nan=True)
+    one = extract_curve_values(list(g["sci"]), xs[2], ys[2])
+    assert one.shape == (len(g["times"]),) and np.array_equal(one, g["curve_values_one"], equal_nan=True)
+    with pytest.raises(ValueError):
+        extract_curve_values(g["sci"], xs[:, :-1], ys[:, :-1])
+
+
 @pytest.mark.gpu
 def test_gpu_coadds_bit_exact(golden):
     from kbmod_b200.stamp_filters import coadd_stamps
