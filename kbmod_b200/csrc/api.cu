@@ -91,6 +91,13 @@ struct kb_stack_s {
     DevBuf<float> d_vx, d_vy;
     DevBuf<Slot> d_slots, d_pairs;
     std::string search_note;   // why the last search did not run on the tiled kernel (empty when it did)
+    // The schedule of the tiled kernel depends on the candidate list, not on the start bounds' extent: repeated
+    // searches with the same candidates (row bands, repeated steps) reuse it instead of rebuilding and re-uploading it.
+    TiledPlan *plan_cache = nullptr;
+    std::vector<float> plan_vx, plan_vy;
+    kb_params plan_params{};
+    const void *plan_screen = nullptr;
+    float plan_steps[2] = {0.0f, 0.0f};
     uint64_t n_slots = 0;
     kb_params last_params{};
     bool have_slots = false;
@@ -443,6 +450,7 @@ static void destroy_handle(kb_handle h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->host_thread.joinable()) h->host_thread.join();
+    if (h->plan_cache) tiled_plan_destroy(h->plan_cache);
     if (h->d_raw) cudaFree(h->d_raw);
     if (h->host_stream) cudaStreamDestroy(h->host_stream);
     free_device_stack(h);
@@ -1043,7 +1051,30 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     bool use_pairs = false;
     h->search_note.clear();
     if (h->kernel_mode == 0 || h->kernel_mode == 2) {
-        plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data());
+        const bool hit = h->plan_cache && h->plan_vx.size() == n_cand && h->plan_screen == sv.screen &&
+                         h->plan_steps[0] == sv.q_step_psi && h->plan_steps[1] == sv.q_step_phi &&
+                         h->plan_params.x_start_min == p.x_start_min &&
+                         h->plan_params.results_per_pixel == p.results_per_pixel &&
+                         h->plan_params.do_sigmag_filter == p.do_sigmag_filter &&
+                         memcmp(&h->plan_params.min_lh, &p.min_lh, sizeof(float)) == 0 &&
+                         (n_cand == 0 || (memcmp(h->plan_vx.data(), vx, sizeof(float) * n_cand) == 0 &&
+                                          memcmp(h->plan_vy.data(), vy, sizeof(float) * n_cand) == 0));
+        if (hit) {
+            plan = h->plan_cache;
+        } else {
+            if (h->plan_cache) tiled_plan_destroy(h->plan_cache);
+            h->plan_cache = nullptr;
+            plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data());
+            if (plan) {
+                h->plan_cache = plan;
+                h->plan_vx.assign(vx, vx + n_cand);
+                h->plan_vy.assign(vy, vy + n_cand);
+                h->plan_params = p;
+                h->plan_screen = sv.screen;
+                h->plan_steps[0] = sv.q_step_psi;
+                h->plan_steps[1] = sv.q_step_phi;
+            }
+        }
         if (!plan && h->kernel_mode == 2) throw Error("tiled kernel not usable: " + why);
     } else {
         why = h->kernel_mode == 1 ? "generic kernel requested" : "candidate-parallel kernel requested";
@@ -1052,8 +1083,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     // (pixel, candidate) pairs over the device instead
     const uint64_t n_tiles = ((sw + 63) / 64) * ((sh + 14) / 15);
     if (plan && h->kernel_mode == 0 && n_tiles < 37 && search_pairs_usable(p, n_cand, nullptr)) {
-        tiled_plan_destroy(plan);
-        plan = nullptr;
+        plan = nullptr;   // stays in the cache
         why = "the start window covers only " + std::to_string(n_tiles) + " tiles of the tiled kernel";
     }
     if (!plan && (h->kernel_mode == 3 || (h->kernel_mode == 0 && (p.results_per_pixel > (uint32_t)kMaxRegK || n_tiles < 37)))) {
@@ -1074,14 +1104,23 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     try {
         if (pipelined && !plan)  // the generic kernel reads any row: wait for the whole stack
             KB_CUDA(cudaStreamWaitEvent(st, h->up.ev[h->up.n_chunks - 1], 0));
-        if (plan)
+        if (plan) {
+            bool overflowed = false;
             sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st,
-                                     pipelined ? &h->up : nullptr);
+                                     pipelined ? &h->up : nullptr, &overflowed);
+            if (overflowed) {   // never seen; the generic kernel gives the same slots, slowly
+                h->search_note = "generic kernel used: the request queue of the tiled kernel overflowed";
+                if (pipelined) KB_CUDA(cudaStreamWaitEvent(st, h->up.ev[h->up.n_chunks - 1], 0));
+                sl += launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
+                plan = nullptr;
+            }
+        }
         else if (use_pairs)
             sl = launch_search_pairs(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, h->d_pairs.p, h->scratch, st);
         else sl = launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);
     } catch (...) {
-        if (plan) tiled_plan_destroy(plan);
+        if (h->plan_cache) tiled_plan_destroy(h->plan_cache);   // do not trust a schedule whose launch failed
+        h->plan_cache = nullptr;
         throw;
     }
     t_search.stop(st);
@@ -1092,8 +1131,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_post.start(st);
     uint64_t n_keep = 0;
     launches += filter_count(h->d_slots.p, n_slots, p.min_lh, p.min_observations, h->scratch, &n_keep, st);
-    const float main_ms = plan ? tiled_plan_kernel_ms(plan) : -1.0f;
-    if (plan) tiled_plan_destroy(plan);  // the stream is idle here (filter_count synchronised)
+    const float main_ms = plan ? tiled_plan_kernel_ms(plan) : -1.0f;   // the stream is idle (filter_count synchronised)
     h->d_results.ensure(std::max<uint64_t>(n_keep, 1));
     bool invalid = false;
     launches += filter_finish(h->d_slots.p, n_slots, n_keep, (int)p.results_per_pixel, (int)sw, p.x_start_min,

@@ -97,12 +97,22 @@ struct ClipSurvivor {
     float lh, flux;
     int obs;
 };
+// sigma-G off: a candidate whose upper bound of lh reached the pixel's bar during the sweep, for exact_kernel
+struct __align__(16) ExactReq {
+    uint32_t pixel;  // start-pixel index yi * search_width + xi
+    int cand;
+    float ub;        // upper bound of the candidate's lh from the screening sums
+    uint32_t pad;
+};
 struct ClipScratch {
-    uint2 *queue = nullptr;  // {pixel, candidate}
+    void *queue = nullptr;   // sigma-G on: uint2 {pixel, candidate}; off: ExactReq
+    size_t queue_bytes = 0;
     ClipSurvivor *surv = nullptr;
-    unsigned long long *counters = nullptr;  // [0] requests (may exceed cap), [1] survivors, [2] clipped in line
-    uint64_t cap = 0;       // queue capacity (requests)
+    unsigned long long *counters = nullptr;  // [0] requests (may exceed cap), [1] survivors, [2] evaluated in line
+    uint64_t cap = 0;       // queue capacity (requests) of the current search
     uint64_t surv_cap = 0;  // survivor capacity; the clip kernel is rerun with a larger buffer if it overflows
+    float *bar = nullptr;   // sigma-G off: final bar of every start pixel (its 8th largest lower bound of lh)
+    uint64_t bar_cap = 0;
 };
 void clip_scratch_free(ClipScratch &c);
 struct ResultScratch;
@@ -128,7 +138,7 @@ struct UploadProgress {
 };
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
                         const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st,
-                        const UploadProgress *up = nullptr);
+                        const UploadProgress *up = nullptr, bool *overflowed = nullptr, bool is_chunk = false);
 void tiled_plan_destroy(TiledPlan *plan);
 float tiled_plan_kernel_ms(TiledPlan *plan);  // duration of the gather kernel of the last launch (CUDA events)
 
@@ -170,7 +180,8 @@ struct ResultScratch {
     uint32_t *vals[2] = {nullptr, nullptr};
     uint32_t *block_counts = nullptr;  // compaction
     uint32_t *hist = nullptr;          // radix histograms
-    uint64_t cap_items = 0, cap_blocks = 0, cap_hist = 0;
+    uint32_t *scan_tmp = nullptr;      // tile sums of the multi-CTA scan
+    uint64_t cap_items = 0, cap_blocks = 0, cap_hist = 0, cap_scan_tmp = 0;
     uint32_t *d_count = nullptr;  // number of survivors
     uint32_t *d_flag = nullptr;   // invalid-trajectory flag
 };

@@ -6,6 +6,8 @@
 // Ties in lh keep slot order (y, x, rank): deterministic, where the reference's parallel sort is not.
 #include <float.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace kb {
@@ -97,6 +99,74 @@ __global__ void __launch_bounds__(1024) scan_kernel(uint32_t *data, uint64_t n, 
         __syncthreads();
     }
     if (threadIdx.x == 0 && total_out) *total_out = s_carry;
+}
+
+// Large inputs (radix histograms of many-million-item sorts): three steps over tiles of 8192 words -- tile sums, an
+// exclusive scan of the tile sums by the single-CTA kernel above, and a per-tile scan seeded with its tile's offset.
+static constexpr int ST_ITEMS = 8, ST_TILE = 1024 * ST_ITEMS;
+__global__ void __launch_bounds__(1024) scan_tile_sums_kernel(const uint32_t *__restrict__ data, uint64_t n,
+                                                              uint32_t *__restrict__ tile_sums) {
+    __shared__ uint32_t s_warp[32];
+    const uint64_t base = (uint64_t)blockIdx.x * ST_TILE;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int j = 0; j < ST_ITEMS; ++j) {
+        const uint64_t i = base + (uint64_t)j * 1024 + threadIdx.x;
+        if (i < n) acc += data[i];
+    }
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        uint32_t v = s_warp[threadIdx.x];
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        if (threadIdx.x == 0) tile_sums[blockIdx.x] = v;
+    }
+}
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(uint32_t *data, uint64_t n, const uint32_t *__restrict__ tile_offsets) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = tile_offsets[blockIdx.x];
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint64_t tile0 = (uint64_t)blockIdx.x * ST_TILE;
+    for (int j = 0; j < ST_ITEMS; ++j) {
+        const uint64_t i = tile0 + (uint64_t)j * 1024 + threadIdx.x;
+        const uint32_t v = (i < n) ? data[i] : 0u;
+        uint32_t inc = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if ((int)lane >= d) inc += t;
+        }
+        if (lane == 31) s_warp[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            uint32_t ws = s_warp[lane], winc = ws;
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, winc, d);
+                if ((int)lane >= d) winc += t;
+            }
+            s_warp[lane] = winc - ws;
+        }
+        __syncthreads();
+        const uint32_t excl = s_carry + s_warp[w] + inc - v;
+        if (i < n) data[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+}
+
+// In-place exclusive scan of n words; `tmp` holds one word per 8192-word tile (only used for large n).
+static void scan_u32(uint32_t *data, uint64_t n, uint32_t *total_out, uint32_t *tmp, uint64_t tmp_words, cudaStream_t st) {
+    const uint64_t tiles = (n + ST_TILE - 1) / ST_TILE;
+    if (n <= 4 * (uint64_t)ST_TILE || !tmp || tiles > tmp_words) {
+        scan_kernel<<<1, 1024, 0, st>>>(data, n, total_out);
+        return;
+    }
+    scan_tile_sums_kernel<<<(unsigned)tiles, 1024, 0, st>>>(data, n, tmp);
+    scan_kernel<<<1, 1024, 0, st>>>(tmp, tiles, total_out);
+    scan_tiles_kernel<<<(unsigned)tiles, 1024, 0, st>>>(data, n, tmp);
 }
 
 __global__ void __launch_bounds__(CB)
@@ -206,7 +276,7 @@ static int radix_sort_pairs(ResultScratch &scr, uint64_t n, cudaStream_t st) {
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = pass * 8;
         radix_hist_kernel<<<nblocks, RB, 0, st>>>(scr.keys[cur], n, shift, scr.hist, nblocks);
-        scan_kernel<<<1, 1024, 0, st>>>(scr.hist, (uint64_t)256 * nblocks, nullptr);
+        scan_u32(scr.hist, (uint64_t)256 * nblocks, nullptr, scr.scan_tmp, scr.cap_scan_tmp, st);
         radix_scatter_kernel<<<nblocks, RB, 0, st>>>(scr.keys[cur], scr.vals[cur], n, shift, scr.hist, nblocks,
                                                      scr.keys[cur ^ 1], scr.vals[cur ^ 1]);
         cur ^= 1;
@@ -275,6 +345,13 @@ static void ensure_scratch(ResultScratch &s, uint64_t items, uint64_t cblocks) {
         KB_CUDA(cudaMalloc(&s.hist, sizeof(uint32_t) * need_hist));
         s.cap_hist = need_hist;
     }
+    const uint64_t need_tmp = std::max<uint64_t>(need_hist, cblocks) / ST_TILE + 2;
+    if (need_tmp > s.cap_scan_tmp) {
+        if (s.scan_tmp) cudaFree(s.scan_tmp);
+        s.scan_tmp = nullptr;
+        KB_CUDA(cudaMalloc(&s.scan_tmp, sizeof(uint32_t) * need_tmp));
+        s.cap_scan_tmp = need_tmp;
+    }
 }
 
 void result_scratch_reserve(ResultScratch &s, uint64_t items) { ensure_scratch(s, items, 1); }
@@ -287,6 +364,7 @@ void result_scratch_free(ResultScratch &s) {
     }
     if (s.block_counts) cudaFree(s.block_counts);
     if (s.hist) cudaFree(s.hist);
+    if (s.scan_tmp) cudaFree(s.scan_tmp);
     if (s.d_count) cudaFree(s.d_count);
     if (s.d_flag) cudaFree(s.d_flag);
     s = ResultScratch();
@@ -298,7 +376,7 @@ int filter_count(const Slot *d_slots, uint64_t n_slots, float min_lh, int min_ob
     const uint64_t cblocks = (n_slots + C_TILE - 1) / C_TILE;
     ensure_scratch(scr, 0, cblocks);
     count_kernel<<<(unsigned)cblocks, CB, 0, st>>>(d_slots, n_slots, min_lh, min_obs, scr.block_counts);
-    scan_kernel<<<1, 1024, 0, st>>>(scr.block_counts, cblocks, scr.d_count);
+    scan_u32(scr.block_counts, cblocks, scr.d_count, scr.scan_tmp, scr.cap_scan_tmp, st);
     uint32_t h_count = 0;
     KB_CUDA(cudaMemcpyAsync(&h_count, scr.d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     KB_CUDA(cudaStreamSynchronize(st));
@@ -486,6 +564,7 @@ int merge_clip_survivors(const ClipSurvivor *d_surv, uint64_t n, Slot *d_slots, 
 
 void clip_scratch_free(ClipScratch &c) {
     if (c.queue) cudaFree(c.queue);
+    if (c.bar) cudaFree(c.bar);
     if (c.surv) cudaFree(c.surv);
     if (c.counters) cudaFree(c.counters);
     c = ClipScratch();

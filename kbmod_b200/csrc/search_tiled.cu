@@ -355,11 +355,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     return plan.release();
 }
 
-float tiled_plan_kernel_ms(TiledPlan *plan) {
-    float ms = 0.0f;
-    if (plan && plan->ev1 && cudaEventSynchronize(plan->ev1) == cudaSuccess) cudaEventElapsedTime(&ms, plan->ev0, plan->ev1);
-    return ms;
-}
+float tiled_plan_kernel_ms(TiledPlan *plan) { return plan ? plan->ms_accum : 0.0f; }
 
 void tiled_plan_destroy(TiledPlan *plan) {
     if (!plan) return;
@@ -382,26 +378,57 @@ static void launch_tiled_any(TiledPlan *plan, const StackView &sv, const kb_para
     KB_CUDA(cudaGetLastError());
 }
 
+static constexpr uint64_t kExactQueueCap = 768ull << 20;   // sigma-G off: requests per launch (12 GB of the 180)
+
 int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
                         const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st,
-                        const UploadProgress *up) {
+                        const UploadProgress *up, bool *overflowed, bool is_chunk) {
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
+    if (!is_chunk) {
+        plan->ms_accum = 0.0f;
+        if (overflowed) *overflowed = false;
+    }
+    if (!plan->sigmag && !up && !is_chunk) {
+        // Sigma-G off: every pixel queues the candidates whose bound reached its rising bar -- a few hundred per pixel,
+        // more for longer candidate lists.  A search area whose requests would not fit the queue is searched in
+        // chunks of rows, each with its own exact evaluation and merge.
+        const double n_cand = (double)std::max(plan->v.n_groups * TG, 2);
+        const double per_pixel = 64.0 + 24.0 * log2(n_cand);
+        int rows = (int)std::min<double>((double)sh, std::max(1.0, (double)kExactQueueCap / (per_pixel * (double)sw)));
+        rows = std::max(TBY, rows / TBY * TBY);
+        if (rows < sh) {
+            int launches = 0;
+            for (int ya = p.y_start_min; ya < p.y_start_max; ya += rows) {
+                kb_params pc = p;
+                pc.y_start_min = ya;
+                pc.y_start_max = std::min(p.y_start_max, ya + rows);
+                launches += launch_search_tiled(plan, sv, pc, d_vx, d_vy,
+                                                d_slots + (size_t)(ya - p.y_start_min) * sw * p.results_per_pixel, clip, scr,
+                                                st, nullptr, overflowed, true);
+            }
+            return launches;
+        }
+    }
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
     if (grid.y > 65535) throw Error("search area too tall for the tiled kernel grid");
-    if (plan->sigmag) {
-        // Queue for the deferred clips: every (pixel, candidate) pair if that is small, else 256M requests (2 GB of
-        // the 180 GB); the kernel clips in line once the queue is full, so the capacity only affects speed (C4 with
-        // 20 bright movers raises 108M requests).  Survivors are a small fraction: their buffer starts at 1/8.
-        const uint64_t want = std::min<uint64_t>((uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * TG, 1),
-                                                 256ull << 20);
+    {
+        // Queue of the deferred exact evaluations.  Sigma-G on: {pixel, candidate} of everything whose bound reaches
+        // min_lh (C4 with 20 bright movers raises 108M requests); off: every candidate whose upper bound reached the
+        // pixel's rising bar, with that bound (a few hundred per pixel).  Every (pixel, candidate) pair if that is
+        // small, else a fixed share of the 180 GB; past a full queue the kernel evaluates in line, so the capacity
+        // only affects speed.  Survivors are a small fraction: their buffer starts at 1/8 (it grows on demand).
+        const uint64_t all_pairs = (uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * TG, 1);
+        const size_t elem = plan->sigmag ? sizeof(uint2) : sizeof(ExactReq);
+        const uint64_t want = std::min<uint64_t>(all_pairs, plan->sigmag ? (256ull << 20) : kExactQueueCap);
         if (!clip.counters) KB_CUDA(cudaMalloc(&clip.counters, 4 * sizeof(unsigned long long)));
-        if (clip.cap < want) {
+        if (clip.queue_bytes < want * elem) {
             if (clip.queue) cudaFree(clip.queue);
             clip.queue = nullptr;
-            clip.cap = 0;
-            KB_CUDA(cudaMalloc(&clip.queue, sizeof(uint2) * want));
-            clip.cap = want;
+            clip.queue_bytes = 0;
+            KB_CUDA(cudaMalloc(&clip.queue, want * elem));
+            clip.queue_bytes = want * elem;
         }
+        clip.cap = want;
         const uint64_t want_surv = std::min<uint64_t>(want, std::max<uint64_t>(want / 8, 4ull << 20));
         if (clip.surv_cap < want_surv) {
             if (clip.surv) cudaFree(clip.surv);
@@ -410,8 +437,17 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
             KB_CUDA(cudaMalloc(&clip.surv, sizeof(ClipSurvivor) * want_surv));
             clip.surv_cap = want_surv;
         }
+        if (!plan->sigmag && clip.bar_cap < (uint64_t)sw * sh) {
+            if (clip.bar) cudaFree(clip.bar);
+            clip.bar = nullptr;
+            clip.bar_cap = 0;
+            KB_CUDA(cudaMalloc(&clip.bar, sizeof(float) * (uint64_t)sw * sh));
+            clip.bar_cap = (uint64_t)sw * sh;
+        }
         KB_CUDA(cudaMemsetAsync(clip.counters, 0, 4 * sizeof(unsigned long long), st));
-        plan->v.clipq = clip.queue;
+        plan->v.clipq = plan->sigmag ? static_cast<uint2 *>(clip.queue) : nullptr;
+        plan->v.exq = plan->sigmag ? nullptr : static_cast<ExactReq *>(clip.queue);
+        plan->v.bar_out = clip.bar;
         plan->v.clip_cnt = clip.counters;
         plan->v.clip_cap = clip.cap;
     }
@@ -461,19 +497,31 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         KB_CUDA(cudaStreamWaitEvent(st, up->ev[up->n_chunks - 1], 0));  // clips and the epilogue read any row
     }
     KB_CUDA(cudaEventRecord(plan->ev1, st));
-    if (plan->sigmag) {
+    {
         unsigned long long cnt[4];
         for (int attempt = 0; attempt < 2; ++attempt) {
-            switch (sv.nb) {
-                case 4: launch_clip_nb4(sv, p, d_vx, d_vy, clip, st); break;
-                case 2: launch_clip_nb2(sv, p, d_vx, d_vy, clip, st); break;
-                default: launch_clip_nb1(sv, p, d_vx, d_vy, clip, st); break;
+            if (plan->sigmag) {
+                switch (sv.nb) {
+                    case 4: launch_clip_nb4(sv, p, d_vx, d_vy, clip, st); break;
+                    case 2: launch_clip_nb2(sv, p, d_vx, d_vy, clip, st); break;
+                    default: launch_clip_nb1(sv, p, d_vx, d_vy, clip, st); break;
+                }
+            } else {
+                switch (sv.nb) {
+                    case 4: launch_exact_nb4(sv, p, d_vx, d_vy, clip, st); break;
+                    case 2: launch_exact_nb2(sv, p, d_vx, d_vy, clip, st); break;
+                    default: launch_exact_nb1(sv, p, d_vx, d_vy, clip, st); break;
+                }
             }
             ++launches;
             KB_CUDA(cudaMemcpyAsync(cnt, clip.counters, sizeof(cnt), cudaMemcpyDeviceToHost, st));
             KB_CUDA(cudaStreamSynchronize(st));
+            if (attempt == 0) {   // the stream is idle: the gather kernel's events have fired
+                float ms = 0.0f;
+                if (cudaEventElapsedTime(&ms, plan->ev0, plan->ev1) == cudaSuccess) plan->ms_accum += ms;
+            }
             if (cnt[1] <= clip.surv_cap) break;
-            // more survivors than the buffer holds: enlarge it and clip the (intact) queue again
+            // more survivors than the buffer holds: enlarge it and work the (intact) queue off again
             cudaFree(clip.surv);
             clip.surv = nullptr;
             clip.surv_cap = 0;
@@ -482,9 +530,10 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
             KB_CUDA(cudaMemsetAsync(clip.counters + 1, 0, sizeof(unsigned long long), st));
         }
         if (getenv("KB_DEBUG"))
-            fprintf(stderr, "[kbmod_b200] sigma-G clips: requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
-                    cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
+            fprintf(stderr, "[kbmod_b200] deferred exact evaluations (%s): requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
+                    plan->sigmag ? "sigma-G clips" : "bounds reached the bar", cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
         launches += merge_clip_survivors(clip.surv, cnt[1], d_slots, (int)p.results_per_pixel, scr, st);
+        if (!plan->sigmag && cnt[3] && overflowed) *overflowed = true;   // a full queue dropped requests
     }
     return launches;
 }

@@ -78,6 +78,10 @@ struct PlanView {
     // scaled by 0.99999), bar_ok = 0 when min_lh is not a positive squarable number (then nothing is screened out)
     float bar_c3, bar_c4;
     int bar_ok;
+    // sigma-G off: requests for the deferred exact evaluation {pixel, candidate, upper bound of lh} (the counters and
+    // the capacity are clip_cnt / clip_cap), and every pixel's final bar (its 8th largest lower bound)
+    ExactReq *exq;
+    float *bar_out;
 };
 
 struct TiledPlan {
@@ -85,6 +89,7 @@ struct TiledPlan {
     PlanView v{};
     void *d_block = nullptr;  // one allocation holding all tables
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the gather kernel
+    float ms_accum = 0.0f;    // gather-kernel time of the last search (summed over its chunks)
     size_t smem = 0;
     int reach_hi = 0;  // a tile at row y0 reads stack rows below y0 + reach_hi (largest box bottom, padded)
     int nb = 4, K = 8;
@@ -149,6 +154,20 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     return w;
 }
 
+// bounds of the reference's lh = psi_sum / sqrt(phi_sum) (-1 for phi_sum <= 0) from the bounds of the two sums; the
+// 4e-6 covers MUFU.RSQ and the reference's own division and square-root roundings
+__device__ __forceinline__ void lh_bounds(float ps, float ph, float e_psi, float e_phi, float &lb, float &ub) {
+    const float psi_hi = ps + e_psi, psi_lo = ps - e_psi, phi_hi = ph + e_phi, phi_lo = ph - e_phi;
+    if (!(phi_lo > 0.0f)) {   // phi_sum may be <= 0 (lh = -1) or tiny (lh huge): no bounds
+        lb = -CUDART_INF_F;
+        ub = CUDART_INF_F;
+        return;
+    }
+    const float rl = rsqrtf(phi_lo), rh = rsqrtf(phi_hi);
+    ub = (psi_hi >= 0.0f) ? psi_hi * rl * 1.000004f : psi_hi * rh * 0.999996f;
+    lb = (psi_lo >= 0.0f) ? psi_lo * rh * 0.999996f : psi_lo * rl * 1.000004f;
+}
+
 // ---- the kernel -----------------------------------------------------------------------------------------
 // The gather loop works on the SCREENING copy of the stack (StackView::screen): one 32-bit word per pixel pair, psi
 // and phi as signed 16-bit multiples of sv.q_step_psi / sv.q_step_phi, 0 for an invalid pair (and for everything
@@ -162,6 +181,11 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
 // evaluated EXACTLY from the search copy with the reference's own arithmetic: through the deferred clip queue when
 // sigma-G is on (clip_kernel re-gathers, checks the unclipped likelihood, clips), in line otherwise.  The result is
 // therefore identical to evaluating every candidate exactly; the screening only decides how much work that takes.
+// With sigma-G off the bar is the pixel's K-th best lh, which only exact evaluation knows; the sweep uses bounds
+// instead: the 8th largest LOWER bound seen so far is a valid bar (eight candidates are known to reach it), and a
+// candidate whose UPPER bound reaches the bar is queued with that bound.  exact_kernel afterwards evaluates the
+// queued candidates whose bound still reaches the pixel's final bar -- about ten per pixel -- and the survivors are
+// merged into the slots by (lh, candidate index).
 // NB is the encoding of the exact search copy (4 = float, 2 = uint16, 1 = uint8), used by the exact routines only.
 // COUNT: keep a per-candidate observation count (sigma-G off and min_obs > 0), so candidates with too few
 // observations are dropped before the exact evaluation.
@@ -248,9 +272,14 @@ __global__ void __launch_bounds__(TNT, 1)
         int P[TPX][TG], F[TPX][TG];
         int cnt[COUNT ? TPX : 1][COUNT ? TG : 1];
         TopK<K> top[TPX];
+        float lb8[SIGMAG ? 1 : TPX][8];   // sigma-G off: the 8 largest lower bounds of lh so far, descending
 #pragma unroll
         for (int h = 0; h < TPX; ++h) {
-            top[h].init();
+            if (SIGMAG) top[h].init();   // sigma-G off: the lists are not touched before the sweep is over
+            if (!SIGMAG) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) lb8[h][i] = -CUDART_INF_F;
+            }
 #pragma unroll
             for (int j = 0; j < TG; ++j) {
                 P[h][j] = 0;
@@ -286,7 +315,13 @@ __global__ void __launch_bounds__(TNT, 1)
                         for (int h = 0; h < TPX; ++h) {
                             P[h][j] = __dp2a_lo((int)w[h], 0x0001, P[h][j]);   // += low half  (psi, signed 16 bit)
                             F[h][j] = __dp2a_lo((int)w[h], 0x0100, F[h][j]);   // += high half (phi)
-                            if (COUNT) cnt[h][j] += (w[h] != 0u) ? 1 : 0;  // the quantiser never maps a valid pair to 0
+                            if (COUNT) {
+                                // valid <=> word != 0 (the quantiser never maps a valid pair to 0): one compare and
+                                // one predicated add in place (the compiler's select form costs a move more)
+                                asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}"
+                                    : "+r"(cnt[h][j])
+                                    : "r"(w[h]));
+                            }
                         }
                     }
                 }
@@ -313,7 +348,7 @@ __global__ void __launch_bounds__(TNT, 1)
                         c4 = pv.bar_c4;
                         screen = pv.bar_ok != 0;
                     } else {
-                        const float bar = top[h].worst();
+                        const float bar = lb8[h][7];
                         screen = bar > 0.0f && bar < 1.0e15f;
                         const float b2 = bar * bar * 0.99999f;
                         c3 = pv.step_phi * b2;
@@ -321,8 +356,9 @@ __global__ void __launch_bounds__(TNT, 1)
                     }
 #pragma unroll
                     for (int j = 0; j < TG; ++j) {
-                        const float t = fmaf(__int2float_rn(P[h][j]), pv.step_psi, pv.e_psi);
-                        const float r = fmaf(__int2float_rn(F[h][j]), c3, c4);
+                        const float Pf = __int2float_rn(P[h][j]), Ff = __int2float_rn(F[h][j]);
+                        const float t = fmaf(Pf, pv.step_psi, pv.e_psi);
+                        const float r = fmaf(Ff, c3, c4);
                         P[h][j] = 0;
                         F[h][j] = 0;
                         bool alive = in_bounds[h] && (!screen || (t > 0.0f && t * t >= r));
@@ -330,13 +366,51 @@ __global__ void __launch_bounds__(TNT, 1)
                             alive = alive && cnt[h][j] >= p.min_observations;   // kernels.cu:318 obs_count < min_obs
                             cnt[h][j] = 0;
                         }
-                        passmask |= alive ? (1u << (h * TG + j)) : 0u;
+                        if (SIGMAG) {
+                            passmask |= alive ? (1u << (h * TG + j)) : 0u;
+                        } else {
+                            // sigma-G off: raise the pixel's bar with the candidate's lower bound and queue the
+                            // candidate with its upper bound for the exact evaluation after the sweep
+                            const unsigned am = __ballot_sync(0xffffffffu, alive);
+                            if (am) {
+                                const int c = __ldg(pv.cand + g * TG + j);   // warp-uniform; < 0: padding
+                                float lb, ub;
+                                lh_bounds(Pf * pv.step_psi, Ff * pv.step_phi, pv.e_psi, pv.e_phi, lb, ub);
+                                const bool on = alive && c >= 0;
+                                if (on && lb > lb8[h][7]) {
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) {
+                                        if (lb > lb8[h][i]) {
+                                            const float tmp = lb8[h][i];
+                                            lb8[h][i] = lb;
+                                            lb = tmp;
+                                        }
+                                    }
+                                    const float bar = lb8[h][7];
+                                    screen = bar > 0.0f && bar < 1.0e15f;
+                                    const float b2 = bar * bar * 0.99999f;
+                                    c3 = pv.step_phi * b2;
+                                    c4 = -pv.e_phi * b2;
+                                }
+                                const unsigned qm = __ballot_sync(0xffffffffu, on && ub >= lb8[h][7]);
+                                if (qm) {
+                                    unsigned long long base_slot = 0;
+                                    if (lane == 0) base_slot = atomicAdd(pv.clip_cnt, (unsigned long long)__popc(qm));
+                                    base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
+                                    const unsigned long long slot_q = base_slot + __popc(qm & ((1u << lane) - 1u));
+                                    if ((qm >> lane) & 1u) {
+                                        if (slot_q < pv.clip_cap) pv.exq[slot_q] = ExactReq{pixel_index[h], c, ub, 0u};
+                                        else pv.clip_cnt[3] = 1ull;   // queue full: the host repeats the search
+                                    }
+                                }
+                            }
+                        }
                     }
                 }
-                unsigned wm = passmask;
+                unsigned wm = SIGMAG ? passmask : 0u;
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) wm |= __shfl_xor_sync(0xffffffffu, wm, d);
-                while (wm) {   // warp-uniform loop over the (pixel slot, candidate) pairs some lane still needs
+                while (SIGMAG && wm) {   // warp-uniform loop over the (pixel slot, candidate) pairs some lane needs
                     const int b = __ffs(wm) - 1;
                     wm &= wm - 1;
                     const int h = b / TG, j = b % TG;
@@ -345,22 +419,7 @@ __global__ void __launch_bounds__(TNT, 1)
                     const bool alive = (passmask >> b) & 1u;
                     const int x = (h == 0) ? px[0] : px[TPX - 1];
                     static_assert(TPX <= 2, "pixel selection below handles two pixels per lane");
-                    if (!SIGMAG) {
-                        if (alive) {
-                            float lh, flux;
-                            int obs;
-                            evaluate_exact<NB, false, 1>(sv, s_times, p, x, py, __ldg(cvx + c), __ldg(cvy + c), lh, flux,
-                                                         obs, nullptr);
-                            if (!(obs < p.min_observations)) {
-                                if (h == 0) {
-                                    if (beats(lh, c, top[0].worst(), top[0].cand[K - 1])) top[0].insert(lh, c);
-                                } else {
-                                    if (beats(lh, c, top[TPX - 1].worst(), top[TPX - 1].cand[K - 1]))
-                                        top[TPX - 1].insert(lh, c);
-                                }
-                            }
-                        }
-                    } else {
+                    {
                         // The exact evaluation (unclipped lh against min_lh, then the clip) is deferred: append
                         // (pixel, candidate) to the global queue; clip_kernel works it off afterwards with every SM
                         // (the requests cluster around bright sources).
@@ -398,6 +457,7 @@ __global__ void __launch_bounds__(TNT, 1)
         }
 #pragma unroll
         for (int h = 0; h < TPX; ++h) {
+            if (!SIGMAG) top[h].init();
             // ---- candidates whose offsets could not be tabulated exactly: full per-pixel arithmetic ----------
             for (int e = 0; e < pv.n_exact; ++e) {
                 const int c = __ldg(pv.exact + e);
@@ -410,6 +470,7 @@ __global__ void __launch_bounds__(TNT, 1)
             }
             // ---- epilogue: flux and obs_count of the winners, written in the reference's slot order ------------
             const int xi = px[h] - p.x_start_min, yi = py - p.y_start_min;
+            if (!SIGMAG && in_bounds[h]) pv.bar_out[pixel_index[h]] = lb8[h][7];
 #pragma unroll
             for (int r = 0; r < K; ++r) {
                 if (r >= (int)p.results_per_pixel) break;  // warp-uniform
@@ -470,6 +531,68 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// ---- sigma-G off: exact evaluation of the queued candidates, one warp per request, all SMs -----------------------
+// Lanes take consecutive images (32 gathers in flight); the sums are then taken in time order, which is the
+// reference's order (kernels.cu:175-197), every lane running the same chain on shuffled values.
+template <int NB>
+__global__ void __launch_bounds__(256)
+        exact_kernel(const StackView sv, const kb_params p, const float *__restrict__ cvx, const float *__restrict__ cvy,
+                     const ExactReq *__restrict__ queue, unsigned long long *cnt, unsigned long long cap,
+                     const float *__restrict__ bar, ClipSurvivor *__restrict__ surv, unsigned long long surv_cap) {
+    extern __shared__ double s_times[];
+    for (int i = threadIdx.x; i < sv.T; i += blockDim.x) s_times[i] = sv.times[i];
+    __syncthreads();
+    const unsigned FULL = 0xffffffffu;
+    const unsigned long long n = min(cnt[0], cap);
+    const int sw = p.x_start_max - p.x_start_min;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < n; i += nwarps) {
+        const ExactReq rq = queue[i];
+        const float b = __ldg(bar + rq.pixel);
+        if (!(rq.ub >= b)) continue;   // the pixel's bar rose above this candidate's bound after it was queued
+        const int x = p.x_start_min + (int)(rq.pixel % (unsigned)sw), y = p.y_start_min + (int)(rq.pixel / (unsigned)sw);
+        const float vx = __ldg(cvx + rq.cand), vy = __ldg(cvy + rq.cand);
+        float ps = 0.0f, ph = 0.0f;
+        int seen = 0;
+        for (int t0 = 0; t0 < sv.T; t0 += 32) {
+            const int t = t0 + lane;
+            float a = 0.0f, c = 0.0f;
+            bool ok = false;
+            if (t < sv.T) {
+                const double tm = s_times[t];
+                ok = load_pair<NB>(sv, t, predict_index(y, vy, tm), predict_index(x, vx, tm), a, c);
+            }
+            const unsigned okm = __ballot_sync(FULL, ok);
+            seen += __popc(okm);
+            const int nsrc = min(32, sv.T - t0);
+            for (int ls = 0; ls < nsrc; ++ls) {
+                const float va = __shfl_sync(FULL, a, ls), vc = __shfl_sync(FULL, c, ls);
+                if ((okm >> ls) & 1u) {
+                    ps = __fadd_rn(ps, va);
+                    ph = __fadd_rn(ph, vc);
+                }
+            }
+        }
+        float lh, flux;
+        finish_sums(ps, ph, lh, flux);
+        // kernels.cu:318: obs_count < min_obs never enters the list; a NaN lh never passes the insertion's '>'
+        if (lane == 0 && !(seen < p.min_observations) && lh >= b) {
+            const unsigned long long k = atomicAdd(cnt + 1, 1ull);   // counts past surv_cap too: host reruns
+            if (k < surv_cap) surv[k] = ClipSurvivor{rq.pixel, rq.cand, lh, flux, seen};
+        }
+    }
+}
+
+template <int NB>
+static void launch_exact(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
+                         ClipScratch &clip, cudaStream_t st) {
+    const size_t tbytes = sizeof(double) * (size_t)sv.T;
+    exact_kernel<NB><<<148 * 8, 256, tbytes, st>>>(sv, p, d_vx, d_vy, static_cast<const ExactReq *>(clip.queue), clip.counters,
+                                                   clip.cap, clip.bar, clip.surv, clip.surv_cap);
+    KB_CUDA(cudaGetLastError());
+}
+
 template <int NB>
 static void launch_clip(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy,
                         ClipScratch &clip, cudaStream_t st) {
@@ -477,7 +600,7 @@ static void launch_clip(const StackView &sv, const kb_params &p, const float *d_
     const int grid = 148 * 8;
 #define KB_CLIP(MT)                                                                                              \
     clip_kernel<NB, MT><<<grid, 256, tbytes + ((MT) <= 256 ? sizeof(float2) * 8 * (MT) : 0), st>>>(              \
-            sv, p, d_vx, d_vy, clip.queue, clip.counters, clip.cap, clip.surv, clip.surv_cap)
+            sv, p, d_vx, d_vy, static_cast<const uint2 *>(clip.queue), clip.counters, clip.cap, clip.surv, clip.surv_cap)
     if (sv.T <= 32) KB_CLIP(32);
     else if (sv.T <= 64) KB_CLIP(64);
     else if (sv.T <= 128) KB_CLIP(128);
@@ -527,5 +650,11 @@ void launch_clip_nb2(const StackView &sv, const kb_params &p, const float *d_vx,
                      cudaStream_t st);
 void launch_clip_nb1(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,
                      cudaStream_t st);
+void launch_exact_nb4(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,
+                      cudaStream_t st);
+void launch_exact_nb2(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,
+                      cudaStream_t st);
+void launch_exact_nb1(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,
+                      cudaStream_t st);
 
 }  // namespace kb

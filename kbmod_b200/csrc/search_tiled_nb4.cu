@@ -13,4 +13,9 @@ void launch_clip_nb4(const StackView &sv, const kb_params &p, const float *d_vx,
     launch_clip<4>(sv, p, d_vx, d_vy, clip, st);
 }
 
+void launch_exact_nb4(const StackView &sv, const kb_params &p, const float *d_vx, const float *d_vy, ClipScratch &clip,
+                      cudaStream_t st) {
+    launch_exact<4>(sv, p, d_vx, d_vy, clip, st);
+}
+
 }  // namespace kb
