@@ -2,21 +2,30 @@
 """bench.py -- headline benchmark of the shift-and-stack search (BASELINE.json metric:
 pixel-trajectory-observation evaluations per second).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2|C3u16|C3u8|C1]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2|C3u16|C3u8|C4|C5|C1]
 
 Workload at N=1 (BASELINE.json configs[1], "C2"): FakeDataSet 20 x 2048 x 2048 float32 psi/phi (seed 101, 1 % masks,
 7x7 Gaussian PSF, 20 injected movers), VelocityGridSearch 50 x 40 = 2000 candidates, sigma-G filter on
 (percentiles 25/75, coeff 0.7413, min_lh 10), min_obs 10, results_per_pixel 8.  A "step" is one search_all over
-every start pixel.  For N > 1 (weak scaling) the image is N times taller (2048 x 2048*N), psi/phi is replicated on
-every GPU, rank r searches the start-pixel row band [2048 r, 2048 (r+1)) and the per-GPU sorted results are merged
-by an NCCL all-gather + global sort inside the timed step.
+every start pixel.  For N > 1 (weak scaling) the image is N times taller (2048 x 2048*N), rank r searches the
+start-pixel row band [2048 r, 2048 (r+1)) and builds psi/phi only for the image rows that band can reach; the
+per-GPU sorted results are merged by an NCCL all-gather + rank merge inside the timed step.
 
 value  : whole-job evals/s with psi/phi resident in HBM when the timed region starts (preloaded stack).
-e2e    : the same metric through the public API with host buffers: every step uploads the psi/phi stack from
-         pinned host memory (search_all on a non-preloaded StackSearch, exactly what the reference does in
-         PsiPhiArray::move_to_gpu) and reads the filtered, sorted result list back to the host.
+e2e    : the same metric through the public API with host buffers: every step uploads the psi/phi stack from the
+         (pinned) host copy -- search_all on a StackSearch whose device copy was dropped with
+         unload_psi_phi_array(), exactly what the reference does in PsiPhiArray::move_to_gpu -- and reads the
+         filtered, sorted result list back to the host.
+e2e_with_ctor / e2e_first_search (flat keys): the one-shot pipeline as KBMOD drives the API -- StackSearch(host
+         images) + search_all + get_results, and the search + read part of it.
+roofline: the gather kernel against the shared-memory load peak, measured in this process by kb_measure_peaks
+         together with the L2-resident gather and HBM streaming figures (flat keys frac_* / peak_*).
+parity / reference_gpu (N = 1): the unmodified reference's own CUDA search_all from oracle/_ref on the same GPU --
+         result lists identical modulo exact lh ties, and its time.  merge_check (N > 1): the NCCL-merged list against
+         one GPU searching the whole frame.  named_config (N > 1): BASELINE.json's C4, strong-scaled, ctor included.
 The stack (671 MB at N=1) is larger than the 126 MB L2, so no L2 flush is needed between iterations.
-Only the cpu_baseline leg and --impl reference touch oracle/ (the reference's own CPU search_all).
+Only the cpu_baseline, parity / reference_gpu legs and --impl reference touch oracle/ (the checker and the
+reference's own code), all outside the timed regions of our arm.
 """
 import argparse
 import json
@@ -541,7 +550,9 @@ def run_ours(args, c, cfg_name):
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if os.path.exists(peaks_file) else "fallback (B200_PROFILING.md)"
     nbytes = {-1: 4, 4: 4, 2: 2, 1: 1}[c["nb"]]
     bytes_per_eval = 2 * nbytes
-    smem_key = {4: "smem_lds64", 2: "smem_lds32", 1: "smem_lds16"}[nbytes]
+    # whatever the stack's encoding, the gather loop reads one 32-bit word of the 16-bit fixed-point screening copy per
+    # evaluation (LDS.32): that is the load whose measured peak bounds it
+    smem_key, actual_bytes_per_eval = "smem_lds32", 4
     kernel_ms = k_ms / max(n_kernel, 1)
     achieved = evals_rank * bytes_per_eval / (kernel_ms * 1e-3) / 1e9
     traffic_tab = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -555,10 +566,16 @@ def run_ours(args, c, cfg_name):
                 "traffic": ncu["dram_bytes"] if ncu else None, "traffic_unit": "bytes/launch (dram read + write)",
                 "traffic_source": ncu["source"] if ncu else None,
                 "kernel": kname, "kernel_ms": kernel_ms, "bytes_per_eval": bytes_per_eval,
+                "actual_smem_bytes_per_eval": actual_bytes_per_eval if tiled else None,
+                "frac_actual_bytes": (achieved * actual_bytes_per_eval / bytes_per_eval / bound_peak) if tiled else None,
                 "peak_source": f"kb_measure_peaks in this run: {smem_key} (shared-memory loads of this encoding's "
                                f"pair width on all SMs)" if tiled else "kb_measure_peaks in this run: L2-resident 256 B row gather",
                 "peaks_measured_in_run_gbs": pk, "hbm_copy_peak_gbs": hbm_copy, "hbm_copy_peak_source": hbm_src,
-                "note": "achieved = algorithmic gather bytes (P*N*T pairs x bytes per pair) / gather-kernel time"}
+                "note": "achieved = algorithmic gather bytes (P*N*T pairs x bytes per pair of this encoding) / gather-kernel "
+                        "time.  The kernel screens every evaluation with a 4-byte word of a 16-bit fixed-point copy of "
+                        "the stack (exact integer sums, rigorous bounds) and evaluates exactly only what the bounds "
+                        "cannot rule out, so for float32 stacks (8-byte pairs) the algorithmic fraction can exceed 1; "
+                        "frac_actual_bytes counts the 4 bytes the loop really reads"}
     flat = {"kernel_ms": kernel_ms, "achieved_gbs": achieved,
             "frac_shared_memory": achieved / pk[smem_key], "peak_shared_memory": pk[smem_key],
             "frac_l2_gather": achieved / pk["l2_row_gather_256B"], "peak_l2_gather": pk["l2_row_gather_256B"],
@@ -566,7 +583,8 @@ def run_ours(args, c, cfg_name):
             "wavefronts_per_gather": (ncu["smem_wavefronts"] / (evals_rank / 32.0)) if ncu else None,
             "e2e_first_search_ms": first_ms, "e2e_first_search": evals_job / (first_ms * 1e-3),
             "e2e_with_ctor_ms": with_ctor_ms, "e2e_with_ctor": evals_job / (with_ctor_ms * 1e-3),
-            "ctor_seconds": ctor_s}
+            "ctor_seconds": ctor_s, "storage_dtype": {4: "f32", 2: "u16", 1: "u8"}[nbytes],
+            "first_search_device_ms": {k: first_tm[k] for k in ("ms_h2d", "ms_prepare", "ms_search", "ms_filter_sort", "ms_total")}}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,

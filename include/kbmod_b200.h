@@ -250,7 +250,12 @@ KB_EXPORT int kb_measure_peaks(double *gbps, int n);
  *   - All calls on a device share that one array.  Calls whose GPU work can overlap (different streams, or
  *     different host threads) race on it: issue them on one stream, or order them with events.
  *   - The first call on each device looks up where that device placed the array (cudaGetSymbolAddress).  Make
- *     that first call during set-up, before any CUDA stream capture begins on the device.
+ *     that first call during set-up, before any CUDA stream capture begins on the device.  The CUDA runtime loads
+ *     the library's device code lazily, so the array's 12 MB are claimed on a device at that first call (or at the
+ *     first other kernel of this library's sorting code there), not when the library is dlopen'ed: a caller that
+ *     hands all remaining HBM to its own pool must make the first call before it does so.
+ *   - The looked-up address is remembered per device ordinal for the life of the process; after cudaDeviceReset
+ *     it is stale, and this entry point must not be used again in that process.
  * The work is enqueued on `cuda_stream` (a cudaStream_t passed as void*; NULL = the default stream) and the call
  * returns without waiting for it. */
 #define KB_STATIC_SORT_MAX (1u << 18)

@@ -974,6 +974,9 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     kb_params p = *params;
     const uint64_t sw = (uint64_t)(p.x_start_max - p.x_start_min), sh = (uint64_t)(p.y_start_max - p.y_start_min);
     const uint64_t n_slots = sw * sh * p.results_per_pixel;
+    // 32-bit slot and start-pixel indices downstream (compaction, sort, request queues): refuse before anything is
+    // allocated or searched
+    if (n_slots >= (1ull << 32)) throw Error("Too many result slots for 32-bit indices (start pixels x results_per_pixel).");
     p.total_results = n_slots;
     h->timing = kb_timing{};
     h->timing.evals = sw * sh * n_cand * (uint64_t)h->T;

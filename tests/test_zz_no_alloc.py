@@ -68,3 +68,20 @@ def test_static_sort_rejects_oversized_lists_and_handles_trivial_ones():
     dummy = torch.zeros(64, dtype=torch.uint8, device="cuda")
     rc = lib.kb_sort_trajectories_static(C.c_void_p(dummy.data_ptr()), C.c_uint64((1 << 18) + 1), None)
     assert rc != 0 and b"exceed" in lib.kb_last_error()
+
+
+def test_static_sort_treats_plus_and_minus_zero_as_a_tie():
+    """+0.0 and -0.0 compare equal in the reference's sort, so they must keep their input order like any other tie
+    (and not sort +0 ahead of -0 by their bit patterns)."""
+    torch = pytest.importorskip("torch")
+    from kbmod_b200._lib import TRAJECTORY_DTYPE, lib
+    n = 5000
+    rec = np.zeros(n, dtype=TRAJECTORY_DTYPE)
+    rng = np.random.default_rng(7)
+    rec["lh"] = rng.choice(np.array([0.0, -0.0, 1.5, -2.0], dtype=np.float32), n)
+    rec["x"] = np.arange(n)                       # input position
+    got = _sorted_by_new_entry_point(torch, lib, rec)
+    order = np.argsort(-rec["lh"].astype(np.float64), kind="stable")   # -0.0 == 0.0 for numpy's comparison too
+    assert np.array_equal(got["x"], rec["x"][order])
+    zeros = got[got["lh"] == 0.0]
+    assert np.all(np.diff(zeros["x"]) > 0) and np.signbit(zeros["lh"]).any() and (~np.signbit(zeros["lh"])).any()
