@@ -470,7 +470,7 @@ def run_ours(args, c, cfg_name):
         ws = kb.StackSearch(wsci, wvar, list(stack.psfs), stack.zeroed_times, c["nb"])
         configure(ws, c)
         ws.set_kernel_mode(2)
-        ws.search_all((vx, vy), True)
+        ws.search_all((vx[:64], vy[:64]), True)
         ws.get_results_array()
         del ws
     # N > 1: every rank builds psi/phi only for the image rows its band of start rows can reach (float stacks; the
