@@ -660,7 +660,7 @@ static void check_params(kb_handle h, const kb_params *p) {
 extern "C" {
 
 const char *kb_last_error(void) { return g_last_error.c_str(); }
-const char *kb_version(void) { return "kbmod_b200 0.1 (sm_100a)"; }
+const char *kb_version(void) { return "kbmod_b200 0.2 (sm_100a)"; }
 
 int kb_device_count(int *count) {
     KB_API_BEGIN
@@ -1111,7 +1111,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
             bool overflowed = false;
             sl = launch_search_tiled(plan, sv, p, h->d_vx.p, h->d_vy.p, h->d_slots.p, h->clip, h->scratch, st,
                                      pipelined ? &h->up : nullptr, &overflowed);
-            if (overflowed) {   // never seen; the generic kernel gives the same slots, slowly
+            if (overflowed) {   // a single row of tiles overflowed the request queue: the generic kernel, slowly
                 h->search_note = "generic kernel used: the request queue of the tiled kernel overflowed";
                 if (pipelined) KB_CUDA(cudaStreamWaitEvent(st, h->up.ev[h->up.n_chunks - 1], 0));
                 sl += launch_search_generic(sv, p, h->d_vx.p, h->d_vy.p, n_cand, h->d_slots.p, st);

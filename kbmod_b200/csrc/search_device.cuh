@@ -190,6 +190,22 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     n_valid = n;
     {   // kernels.cu:175-197: the unclipped sums, valid observations in time order (every lane runs the same chain)
         float ups = 0.0f, uph = 0.0f;
+        if (ws) {
+            // through the warp's shared-memory scratch: every observation at its time index, invalid ones as (+0, +0)
+            // -- adding +0 to a sum that started at +0 is an exact no-op -- then one broadcast read per image
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                const int t = e * 32 + lane;
+                if (t < sv.T) ws[t] = ok[e] ? make_float2(a[e], b[e]) : make_float2(0.0f, 0.0f);
+            }
+            __syncwarp();
+            for (int t = 0; t < sv.T; ++t) {
+                const float2 v = ws[t];
+                ups = __fadd_rn(ups, v.x);
+                uph = __fadd_rn(uph, v.y);
+            }
+            __syncwarp();   // ws is written again below
+        } else
 #pragma unroll
         for (int es = 0; es < E; ++es) {
             const int nsrc = min(32, sv.T - es * 32);  // warp-uniform
@@ -206,18 +222,17 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
     // kernels.cu:201-203: too few observations (or none), or an unclipped lh below min_lh -> the clip is skipped
     if (n < min_obs || n == 0 || lh < min_lh) return;
     // rank[e] = position of my element in ascending order (ties: earlier image first).
-    // Fast pass: count the strictly smaller and the equal values (invalid observations travel as NaN, which
-    // compares false both ways).  Without equal values -- the usual case -- the count of smaller ones is the rank.
+    // Fast pass: count the strictly smaller values (invalid observations travel as NaN, which compares false).
+    // Without equal values -- the usual case -- that count is the rank, and the ranks of the n valid observations
+    // are 0 .. n-1, which add up to n (n - 1) / 2; equal values share a (smaller) rank, so any tie lowers the sum.
     int rank[E];
     bool has_tie = false;
     {
         float lcs[E];
-        int n_eq[E];
 #pragma unroll
         for (int e = 0; e < E; ++e) {
             lcs[e] = ok[e] ? lc[e] : KB_NAN_F;
             rank[e] = 0;
-            n_eq[e] = 0;
         }
 #pragma unroll
         for (int es = 0; es < E; ++es) {
@@ -226,14 +241,15 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
             for (int ls = 0; ls < nsrc; ++ls) {
                 const float v = __shfl_sync(FULL, lcs[es], ls);
 #pragma unroll
-                for (int e = 0; e < E; ++e) {
-                    rank[e] += (v < lcs[e]) ? 1 : 0;
-                    n_eq[e] += (v == lcs[e]) ? 1 : 0;
-                }
+                for (int e = 0; e < E; ++e) rank[e] += (v < lcs[e]) ? 1 : 0;
             }
         }
+        int rsum = 0;
 #pragma unroll
-        for (int e = 0; e < E; ++e) has_tie |= ok[e] && n_eq[e] > 1;
+        for (int e = 0; e < E; ++e) rsum += ok[e] ? rank[e] : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) rsum += __shfl_xor_sync(FULL, rsum, d);
+        has_tie = rsum != n * (n - 1) / 2;
     }
     if (__any_sync(FULL, has_tie)) {
         // Slow pass: ranks with the tie rule, then the payload check below.

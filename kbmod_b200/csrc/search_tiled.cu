@@ -94,6 +94,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
         return nullptr;
     };
     const int T = sv.T, K = (int)p.results_per_pixel;
+    const int TG = group_size(p.do_sigmag_filter != 0);   // candidates per group of this schedule
     if (K > kMaxRegK) return no("results_per_pixel > 8");
     if (n_cand == 0) return no("no candidates");
     if (p.do_sigmag_filter && T > kMaxTSigma) return no("too many images for sigma-G");
@@ -224,7 +225,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
 #pragma omp parallel for schedule(dynamic, 8)
     for (int g = 0; g < n_groups; ++g) {
         const int b = group_start[g], n = group_start[g + 1] - b;
-        int dx[TG], dy[TG];
+        int dx[TGMAX], dy[TGMAX];
         for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
         std::vector<StageRec> &out = per_group[g];
         StageRec cur;
@@ -261,7 +262,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             group_reach[g] = std::max(group_reach[g], mny + rows_pad);
             cur.img[nt].slot_off = used;
             cur.img[nt].pitch_bytes = pitch * PB;
-            for (int j = 0; j < TG; ++j)
+            for (int j = 0; j < TGMAX; ++j)
                 cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
             used += bytes;
             tx += bytes;
@@ -291,6 +292,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     plan->nb = sv.nb;
     plan->K = K;
     plan->sigmag = p.do_sigmag_filter != 0;
+    plan->tg = TG;
     auto up = [](size_t b) { return (b + 255) / 256 * 256; };
     const size_t b_st = up(std::max<size_t>(stages.size(), 1) * sizeof(StageRec)), b_cand = up(cand.size() * 4),
                  b_ex = up(std::max<size_t>(exact.size(), 1) * 4);
@@ -392,7 +394,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         // Sigma-G off: every pixel queues the candidates whose bound reached its rising bar -- a few hundred per pixel,
         // more for longer candidate lists.  A search area whose requests would not fit the queue is searched in
         // chunks of rows, each with its own exact evaluation and merge.
-        const double n_cand = (double)std::max(plan->v.n_groups * TG, 2);
+        const double n_cand = (double)std::max(plan->v.n_groups * plan->tg, 2);
         const double per_pixel = 64.0 + 24.0 * log2(n_cand);
         int rows = (int)std::min<double>((double)sh, std::max(1.0, (double)kExactQueueCap / (per_pixel * (double)sw)));
         rows = std::max(TBY, rows / TBY * TBY);
@@ -417,7 +419,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         // pixel's rising bar, with that bound (a few hundred per pixel).  Every (pixel, candidate) pair if that is
         // small, else a fixed share of the 180 GB; past a full queue the kernel evaluates in line, so the capacity
         // only affects speed.  Survivors are a small fraction: their buffer starts at 1/8 (it grows on demand).
-        const uint64_t all_pairs = (uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * TG, 1);
+        const uint64_t all_pairs = (uint64_t)sw * sh * (uint64_t)std::max(plan->v.n_groups * plan->tg, 1);
         const size_t elem = plan->sigmag ? sizeof(uint2) : sizeof(ExactReq);
         const uint64_t want = std::min<uint64_t>(all_pairs, plan->sigmag ? (256ull << 20) : kExactQueueCap);
         if (!clip.counters) KB_CUDA(cudaMalloc(&clip.counters, 4 * sizeof(unsigned long long)));
@@ -532,8 +534,25 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         if (getenv("KB_DEBUG"))
             fprintf(stderr, "[kbmod_b200] deferred exact evaluations (%s): requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
                     plan->sigmag ? "sigma-G clips" : "bounds reached the bar", cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
+        if (cnt[0] > clip.cap) {
+            // The queue was too small and requests were dropped.  Search the two halves of the area again, each with
+            // the whole queue to itself (the slots are simply overwritten); a single row of tiles that still does not
+            // fit -- or an upload in flight, whose bands are already sized -- is left to the caller's fallback.
+            if (!up && sh > TBY) {
+                const int half = std::max(TBY, (sh / 2 + TBY - 1) / TBY * TBY);
+                kb_params pa = p, pb = p;
+                pa.y_start_max = p.y_start_min + half;
+                pb.y_start_min = p.y_start_min + half;
+                launches += launch_search_tiled(plan, sv, pa, d_vx, d_vy, d_slots, clip, scr, st, nullptr, overflowed, true);
+                launches += launch_search_tiled(plan, sv, pb, d_vx, d_vy,
+                                                d_slots + (size_t)half * sw * p.results_per_pixel, clip, scr, st, nullptr,
+                                                overflowed, true);
+                return launches;
+            }
+            if (overflowed) *overflowed = true;
+            return launches;
+        }
         launches += merge_clip_survivors(clip.surv, cnt[1], d_slots, (int)p.results_per_pixel, scr, st);
-        if (!plan->sigmag && cnt[3] && overflowed) *overflowed = true;   // a full queue dropped requests
     }
     return launches;
 }

@@ -20,14 +20,15 @@ namespace kb {
 #ifndef KB_TPX
 #define KB_TPX 2
 #endif
-#ifndef KB_TG
-#define KB_TG 8
-#endif
 static constexpr int TPX = KB_TPX;     // start pixels per lane along x: x, x + 32, ...
 static constexpr int TBX = 32 * TPX;   // tile width
 static constexpr int TBY = KB_TBY;     // tile height (consumer warps); +1 producer warp
 static constexpr int TNT = (TBY + 1) * 32;
-static constexpr int TG = KB_TG;       // candidates per group
+static constexpr int TGMAX = 16;       // most candidates per group (record layouts are sized for it)
+// Candidates per group.  Sixteen halve the per-image and per-stage bookkeeping of the sweep; the sigma-G-off variants
+// also keep eight lower bounds (and, with min_obs > 0, sixteen observation counters) per pixel in registers and stay
+// at eight.
+__host__ __device__ constexpr int group_size(bool sigmag) { return sigmag ? 16 : 8; }
 #ifndef KB_TS
 #define KB_TS 4
 #endif
@@ -48,7 +49,7 @@ static constexpr int kScreenPairBytes = 4;  // one 32-bit word of the screening 
 //          offs[j], the byte offset of candidate j's pixel inside the box relative to the thread's own pixel
 struct ImageRec {
     int slot_off, pitch_bytes, pad[2];
-    int offs[TG];
+    int offs[TGMAX];
 };
 struct StageRec {
     int4 meta;
@@ -65,7 +66,7 @@ struct TmapSet {
 
 struct PlanView {
     const StageRec *stages;  // [n_stages]
-    const int *cand;         // [n_groups][TG]  candidate index or -1
+    const int *cand;         // [n_groups][group size]  candidate index or -1
     const int *exact;        // candidates evaluated by the exact routine
     int n_exact, n_groups, n_stages, w_base, w_step, max_ch, T;
     uint2 *clipq;                   // deferred sigma-G requests {start-pixel index, candidate}
@@ -94,6 +95,7 @@ struct TiledPlan {
     int reach_hi = 0;  // a tile at row y0 reads stack rows below y0 + reach_hi (largest box bottom, padded)
     int nb = 4, K = 8;
     bool sigmag = false;
+    int tg = 8;   // candidates per group of this schedule (group_size(sigmag))
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------------
@@ -216,6 +218,7 @@ __global__ void __launch_bounds__(TNT, 1)
     const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
     const int n_stages = pv.n_stages;
     constexpr int PB = kScreenPairBytes;
+    constexpr int TG = group_size(SIGMAG);
 
     if (warp == TBY) {
         // ===================== producer warp: TMA box loads + the stage record =================================
@@ -275,7 +278,6 @@ __global__ void __launch_bounds__(TNT, 1)
         float lb8[SIGMAG ? 1 : TPX][8];   // sigma-G off: the 8 largest lower bounds of lh so far, descending
 #pragma unroll
         for (int h = 0; h < TPX; ++h) {
-            if (SIGMAG) top[h].init();   // sigma-G off: the lists are not touched before the sweep is over
             if (!SIGMAG) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) lb8[h][i] = -CUDART_INF_F;
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(TNT, 1)
 #pragma unroll
                 for (int j4 = 0; j4 < TG / 4; ++j4) {
                     const int4 o = (j4 == 0) ? lds_v4<16>(rec) : ((j4 == 1) ? lds_v4<32>(rec) : ((j4 == 2) ? lds_v4<48>(rec) : lds_v4<64>(rec)));
-                    static_assert(TG <= 16, "offset loads above cover 16 candidates");
+                    static_assert(TG <= TGMAX && TGMAX == 16, "offset loads above cover 16 candidates");
                     const int off[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
@@ -399,8 +401,9 @@ __global__ void __launch_bounds__(TNT, 1)
                                     base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
                                     const unsigned long long slot_q = base_slot + __popc(qm & ((1u << lane) - 1u));
                                     if ((qm >> lane) & 1u) {
+                                        // past a full queue the request is dropped: the host sees the count exceed
+                                        // the capacity and searches the area again in smaller pieces
                                         if (slot_q < pv.clip_cap) pv.exq[slot_q] = ExactReq{pixel_index[h], c, ub, 0u};
-                                        else pv.clip_cnt[3] = 1ull;   // queue full: the host repeats the search
                                     }
                                 }
                             }
@@ -417,7 +420,6 @@ __global__ void __launch_bounds__(TNT, 1)
                     const int c = __ldg(pv.cand + g * TG + j);
                     if (c < 0) continue;   // padding of an incomplete group
                     const bool alive = (passmask >> b) & 1u;
-                    const int x = (h == 0) ? px[0] : px[TPX - 1];
                     static_assert(TPX <= 2, "pixel selection below handles two pixels per lane");
                     {
                         // The exact evaluation (unclipped lh against min_lh, then the clip) is deferred: append
@@ -428,36 +430,17 @@ __global__ void __launch_bounds__(TNT, 1)
                         if (lane == 0) base_slot = atomicAdd(pv.clip_cnt, (unsigned long long)__popc(am));
                         base_slot = __shfl_sync(0xffffffffu, base_slot, 0);
                         const unsigned long long slot_q = base_slot + __popc(am & ((1u << lane) - 1u));
-                        bool inline_need = false;
-                        if (alive) {
-                            const unsigned pi = (h == 0) ? pixel_index[0] : pixel_index[TPX - 1];
-                            if (slot_q < pv.clip_cap) pv.clipq[slot_q] = make_uint2(pi, (unsigned)c);
-                            else inline_need = true;
-                        }
-                        if (__any_sync(0xffffffffu, inline_need)) {  // queue full: evaluate it here and now
-                            int nv = 0;
-                            float lh = -1.0f, flux = -1.0f;
-                            sigmag_for_lanes<NB, MAXT>(inline_need, sv, s_times, x, py, __ldg(cvx + c), __ldg(cvy + c), p,
-                                                       lh, flux, nv);
-                            if (inline_need) {
-                                atomicAdd(pv.clip_cnt + 2, 1ull);
-                                if (!(nv < p.min_observations) && !(lh < p.min_lh)) {
-                                    if (h == 0) {
-                                        if (beats(lh, c, top[0].worst(), top[0].cand[K - 1])) top[0].insert(lh, c);
-                                    } else {
-                                        if (beats(lh, c, top[TPX - 1].worst(), top[TPX - 1].cand[K - 1]))
-                                            top[TPX - 1].insert(lh, c);
-                                    }
-                                }
-                            }
-                        }
+                        // past a full queue the request is dropped; the host sees the count exceed the capacity and
+                        // searches the area again in smaller pieces
+                        if (alive && slot_q < pv.clip_cap)
+                            pv.clipq[slot_q] = make_uint2((h == 0) ? pixel_index[0] : pixel_index[TPX - 1], (unsigned)c);
                     }
                 }
             }
         }
 #pragma unroll
         for (int h = 0; h < TPX; ++h) {
-            if (!SIGMAG) top[h].init();
+            top[h].init();   // the per-pixel lists are not touched before the sweep is over
             // ---- candidates whose offsets could not be tabulated exactly: full per-pixel arithmetic ----------
             for (int e = 0; e < pv.n_exact; ++e) {
                 const int c = __ldg(pv.exact + e);
