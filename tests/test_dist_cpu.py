@@ -63,3 +63,28 @@ def test_two_rank_shard_and_merge_equals_single_process(tmp_path):
         assert got.tobytes() == want.tobytes(), f"rank {r}: merged list differs from the single-process list"
         top = np.load(tmp_path / f"top_{r}.npy")
         assert top.tobytes() == want[:50].tobytes()
+
+
+def test_band_rows_cover_the_reach_of_a_band():
+    from kbmod_b200.dist import band_rows
+    vy = np.array([-3.5, 0.0, 2.0], dtype=np.float32)
+    times = [0.0, 1.0, 4.0]
+    lo, hi = band_rows((100, 200), vy, times, 1000)
+    assert lo <= 100 - 14 and hi >= 200 + 14 and lo >= 0 and hi <= 1000     # 3.5 px/day * 4 days
+    assert band_rows((0, 50), vy, times, 60) == (0, 60)                       # clamped to the image
+    assert band_rows((10, 20), np.zeros(0, dtype=np.float32), times, 100)[0] <= 10
+
+
+def test_bench_band_inputs_are_consistent_between_ranks():
+    """bench.make_band_inputs (the strong-scaling named config): two ranks that need overlapping rows generate the same
+    pixels for them, without either generating the whole frame."""
+    sys.path.insert(0, ROOT)
+    import bench
+    c = dict(bench.CONFIGS["C4"], H=320, W=96, T=5)
+    a, vx, vy = bench.make_band_inputs(c, (40, 200))
+    b, vx2, _ = bench.make_band_inputs(c, (150, 320))
+    assert len(vx) == 20000 and np.array_equal(vx, vx2)
+    for t in range(5):
+        assert np.array_equal(a.sci[t][150:200], b.sci[t][150:200], equal_nan=True)
+        assert np.array_equal(a.var[t][150:200], b.var[t][150:200], equal_nan=True)
+    assert np.isnan(a.sci[0][40:200]).mean() > 0.003 and a.objects == b.objects
