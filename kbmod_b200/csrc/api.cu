@@ -78,6 +78,7 @@ struct kb_stack_s {
     cudaStream_t host_stream = nullptr;
     bool dev_cache = false;       // d_search / d_screen hold the whole canonical stack (built by the constructor)
     int row_lo = 0, row_hi = 0;   // rows of every image this handle holds (the whole image unless band-limited)
+    bool all_valid = false;       // no invalid pair in the rows this handle holds (constructor's scan)
     bool keep_raw = false;        // enough HBM to keep d_raw for good (psi/phi curves are gathered from it)
     void *d_search = nullptr;  // canonical pitched search copy
     uint32_t *d_screen = nullptr;  // 16-bit fixed-point screening copy of the same pixels (StackView::screen)
@@ -134,6 +135,7 @@ static StackView make_view(kb_handle h) {
     sv.screen = h->d_screen;
     sv.q_step_psi = h->q_step_psi;
     sv.q_step_phi = h->q_step_phi;
+    sv.all_valid = h->all_valid ? 1 : 0;
     return sv;
 }
 
@@ -322,8 +324,8 @@ static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, st));
     const char *nozm = getenv("KB_NO_ZERO_MARKER");
     DevBuf<uint32_t> d_scan;
-    d_scan.ensure(5);
-    uint32_t scan[5];
+    d_scan.ensure(6);
+    uint32_t scan[6];
     launch_scan_raw_rows(d_pairs, h->T, h->H, r0, nr, h->W, d_scan.p, st);
     KB_CUDA(cudaMemcpyAsync(scan, d_scan.p, sizeof(scan), cudaMemcpyDeviceToHost, st));
     KB_CUDA(cudaStreamSynchronize(st));
@@ -331,6 +333,7 @@ static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
     float pmn = 3.402823466e+38F, pmx = -3.402823466e+38F, fmn = pmn, fmx = pmx;
     if (scan[1] <= scan[2]) { pmn = ordered_to_float(scan[1]); pmx = ordered_to_float(scan[2]); }
     if (scan[3] <= scan[4]) { fmn = ordered_to_float(scan[3]); fmx = ordered_to_float(scan[4]); }
+    h->all_valid = scan[5] == 0;   // (an encoded stack has the same invalid pairs: only non-finite values map to code 0)
     void *d_ref = d_pairs;   // reference-layout bytes for the host copy
     if (h->nb == 4) {
         h->zm_known = (scan[0] || (nozm && nozm[0] == '1')) ? 0 : 1;
@@ -1038,6 +1041,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     t_h2d.stop(st);
 
     t_prep.start(st);
+    const double t_host0 = now_s();
     h->d_vx.ensure(std::max<uint64_t>(n_cand, 1));
     h->d_vy.ensure(std::max<uint64_t>(n_cand, 1));
     if (n_cand) {
@@ -1100,6 +1104,9 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
         if (getenv("KB_DEBUG")) fprintf(stderr, "[kbmod_b200] %s\n", h->search_note.c_str());
     }
     if (use_pairs) h->d_pairs.ensure(sw * sh * n_cand);
+    if (getenv("KB_DEBUG"))
+        fprintf(stderr, "[kbmod_b200] search set-up on the host (buffers, schedule%s): %.2f ms\n",
+                plan && plan == h->plan_cache ? "" : " n/a", 1e3 * (now_s() - t_host0));
     t_prep.stop(st);
 
     t_search.start(st);

@@ -62,6 +62,7 @@ struct StackView {
     // multiples of q_step_psi / q_step_phi, invalid pair = 0.  Only the tiled kernel's gather loop reads it.
     const uint32_t *screen;
     float q_step_psi, q_step_phi;
+    int all_valid;   // 1 = no invalid pair anywhere in the rows this stack holds (known from the constructor's scan)
 };
 
 // Per-pixel result slot written by the search kernels: 16 bytes, [pixel][K].
@@ -151,7 +152,8 @@ int launch_convolve(const float *d_img, int H, int W, const float *d_psf, int di
 int launch_psi_phi(const float *d_sci, const float *d_var, int H, int W, const float *d_psf, const float *d_psf2,
                    int dim, float psf_total, float psf2_total, float2 *d_out_pairs, float *d_psi_plane,
                    float *d_phi_plane, cudaStream_t st, int y_write_lo = 0, int y_write_hi = -1);
-// zero-pair flag + per-channel min/max of rows [r0, r0 + nr) of a float stack in reference order: d_out[5]
+// zero-pair flag + per-channel min/max + number of invalid pairs (saturating) of rows [r0, r0 + nr) of a float stack
+// in reference order: d_out[6]
 int launch_scan_raw_rows(const float2 *d_pairs, int T, int H, int r0, int nr, int W, uint32_t *d_out, cudaStream_t st);
 int launch_interleave(const float *d_psi, const float *d_phi, uint64_t n, float2 *d_out, cudaStream_t st);
 // min/max over finite values of both channels: d_mm = {psi_min, psi_max, phi_min, phi_max} as ordered uints.

@@ -220,12 +220,13 @@ __device__ __forceinline__ uint64_t stack_row(uint64_t r, int H, int r0, int nr)
 
 // One pass over rows [r0, r0 + nr) of every image of a freshly built float stack (reference order, unpitched):
 // out[0] = 1 when some pair with both values finite is exactly (0, 0) (then invalid pairs cannot be stored as zeros),
-// out[1..4] = {psi_min, psi_max, phi_min, phi_max} over the finite values of each channel, as ordered uints.
+// out[1..4] = {psi_min, psi_max, phi_min, phi_max} over the finite values of each channel, as ordered uints,
+// out[5] = 1 when some pair is invalid (either value not finite).
 __global__ void scan_raw_rows_kernel(const float2 *__restrict__ pairs, int T, int H, int r0, int nr, int W,
                                      uint32_t *out) {
     const uint64_t total = (uint64_t)T * nr * (uint64_t)W;
     uint32_t mn0 = 0xffffffffu, mx0 = 0u, mn1 = 0xffffffffu, mx1 = 0u;
-    bool hit = false;
+    bool hit = false, bad = false;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
         const float2 v = pairs[stack_row(i / W, H, r0, nr) * (uint64_t)W + i % W];
@@ -241,6 +242,7 @@ __global__ void scan_raw_rows_kernel(const float2 *__restrict__ pairs, int T, in
             mx1 = max(mx1, o);
         }
         hit |= fa && fb && v.x == 0.0f && v.y == 0.0f;
+        bad |= !(fa && fb);
     }
     for (int d = 16; d > 0; d >>= 1) {
         mn0 = min(mn0, __shfl_xor_sync(0xffffffffu, mn0, d));
@@ -248,9 +250,10 @@ __global__ void scan_raw_rows_kernel(const float2 *__restrict__ pairs, int T, in
         mn1 = min(mn1, __shfl_xor_sync(0xffffffffu, mn1, d));
         mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, d));
     }
-    const bool any_hit = __any_sync(0xffffffffu, hit);
+    const bool any_hit = __any_sync(0xffffffffu, hit), any_bad = __any_sync(0xffffffffu, bad);
     if ((threadIdx.x & 31) == 0) {
         if (any_hit) atomicExch(out, 1u);
+        if (any_bad) atomicExch(out + 5, 1u);   // some pair is invalid
         atomicMin(out + 1, mn0);
         atomicMax(out + 2, mx0);
         atomicMin(out + 3, mn1);
@@ -259,7 +262,7 @@ __global__ void scan_raw_rows_kernel(const float2 *__restrict__ pairs, int T, in
 }
 
 int launch_scan_raw_rows(const float2 *d_pairs, int T, int H, int r0, int nr, int W, uint32_t *d_out, cudaStream_t st) {
-    const uint32_t init[5] = {0u, 0xffffffffu, 0u, 0xffffffffu, 0u};
+    const uint32_t init[6] = {0u, 0xffffffffu, 0u, 0xffffffffu, 0u, 0u};
     KB_CUDA(cudaMemcpyAsync(d_out, init, sizeof(init), cudaMemcpyHostToDevice, st));
     if (nr > 0) scan_raw_rows_kernel<<<148 * 8, 256, 0, st>>>(d_pairs, T, H, r0, nr, W, d_out);
     KB_CUDA(cudaGetLastError());

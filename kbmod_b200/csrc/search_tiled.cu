@@ -219,6 +219,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
 
     // ---- stage records, group by group (greedy packing of consecutive images into <= STAGE_BYTES) ---------------
     std::vector<int> group_reach(std::max(n_groups, 1), 0);
+    std::vector<int4> group_ext(std::max(n_groups, 1), make_int4(INT_MAX, INT_MIN, INT_MAX, INT_MIN));
     std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
     std::vector<int> cand((size_t)std::max(n_groups, 1) * TG, -1);
     bool overflow = false;
@@ -260,6 +261,10 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
             if (nt == 0) t0 = t;
             cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 16), used);
             group_reach[g] = std::max(group_reach[g], mny + rows_pad);
+            group_ext[g].x = std::min(group_ext[g].x, mnx);
+            group_ext[g].y = std::max(group_ext[g].y, mnx + pitch);
+            group_ext[g].z = std::min(group_ext[g].z, mny);
+            group_ext[g].w = std::max(group_ext[g].w, mny + rows_pad);
             cur.img[nt].slot_off = used;
             cur.img[nt].pitch_bytes = pitch * PB;
             for (int j = 0; j < TGMAX; ++j)
@@ -334,6 +339,15 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     for (int r : group_reach) reach_hi = std::max(reach_hi, r);
     for (int c : exact) reach_hi = std::max(reach_hi, TBY + (int)ceil(fabs((double)h_vy[c]) * tabs) + 2);
     plan->reach_hi = reach_hi;
+    v.ext_x0 = v.ext_y0 = 0;
+    v.ext_x1 = TBX;
+    v.ext_y1 = TBY;
+    for (int g = 0; g < n_groups; ++g) {
+        v.ext_x0 = std::min(v.ext_x0, group_ext[g].x);
+        v.ext_x1 = std::max(v.ext_x1, group_ext[g].y);
+        v.ext_y0 = std::min(v.ext_y0, group_ext[g].z);
+        v.ext_y1 = std::max(v.ext_y1, group_ext[g].w);
+    }
     v.pixel_base = 0;
 
     // ---- tensor maps over the screening copy: dims (pixels, rows, images) of 32-bit words, one per box width; what

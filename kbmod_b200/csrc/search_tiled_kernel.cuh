@@ -83,6 +83,8 @@ struct PlanView {
     // the capacity are clip_cnt / clip_cap), and every pixel's final bar (its 8th largest lower bound)
     ExactReq *exq;
     float *bar_out;
+    // extent of the schedule's boxes relative to a tile's origin: [ext_x0, ext_x1) x [ext_y0, ext_y1) pixels
+    int ext_x0, ext_x1, ext_y0, ext_y1;
 };
 
 struct TiledPlan {
@@ -168,6 +170,43 @@ __device__ __forceinline__ void lh_bounds(float ps, float ph, float e_psi, float
     const float rl = rsqrtf(phi_lo), rh = rsqrtf(phi_hi);
     ub = (psi_hi >= 0.0f) ? psi_hi * rl * 1.000004f : psi_hi * rh * 0.999996f;
     lb = (psi_lo >= 0.0f) ? psi_lo * rh * 0.999996f : psi_lo * rl * 1.000004f;
+}
+
+// The gather of one stage: for each of its nt images, the words of the lane's TPX pixels for the TG candidates.
+// DO_COUNT also counts the valid observations (word != 0: the quantiser never maps a valid pair to 0) with one compare
+// and one predicated add in place (the compiler's select form costs a move more).
+template <int TG, bool DO_COUNT, int CT>
+__device__ __forceinline__ void gather_images(int nt, uint32_t rec, uint32_t lane_base, int warp, int (&P)[TPX][TG],
+                                              int (&F)[TPX][TG], int (&cnt)[CT][CT == 1 ? 1 : TG]) {
+    constexpr int PB = kScreenPairBytes;
+    for (int k = 0; k < nt; ++k, rec += (uint32_t)sizeof(ImageRec)) {
+        const int2 ir = lds_v2<0>(rec);   // {slot_off, pitch_bytes}
+        const uint32_t bk = lane_base + (uint32_t)ir.x + (uint32_t)(warp * ir.y);
+#pragma unroll
+        for (int j4 = 0; j4 < TG / 4; ++j4) {
+            const int4 o = (j4 == 0) ? lds_v4<16>(rec) : ((j4 == 1) ? lds_v4<32>(rec) : ((j4 == 2) ? lds_v4<48>(rec) : lds_v4<64>(rec)));
+            static_assert(TG <= TGMAX && TGMAX == 16, "offset loads above cover 16 candidates");
+            const int off[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int j = j4 * 4 + q;
+                const uint32_t addr = bk + off[q];
+                uint32_t w[TPX];
+                w[0] = lds_u32<0>(addr);
+                if (TPX > 1) w[TPX - 1] = lds_u32<32 * PB>(addr);
+#pragma unroll
+                for (int h = 0; h < TPX; ++h) {
+                    P[h][j] = __dp2a_lo((int)w[h], 0x0001, P[h][j]);   // += low half  (psi, signed 16 bit)
+                    F[h][j] = __dp2a_lo((int)w[h], 0x0100, F[h][j]);   // += high half (phi)
+                    if (DO_COUNT) {
+                        asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}"
+                            : "+r"(cnt[h][j])
+                            : "r"(w[h]));
+                    }
+                }
+            }
+        }
+    }
 }
 
 // ---- the kernel -----------------------------------------------------------------------------------------
@@ -272,6 +311,10 @@ __global__ void __launch_bounds__(TNT, 1)
             pixel_index[h] = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px[h] - p.x_start_min));
         }
         const uint32_t hdr0 = smem_u32(s_hdr), stage0 = smem_u32(s_stage);
+        // Observations only have to be counted where some can be invalid: a stack with invalid pixels, or a tile from
+        // which some box of the schedule reaches over the image's edge (CTA-uniform).
+        const bool count_here = !(sv.all_valid && tile_x0 + pv.ext_x0 >= 0 && tile_x0 + pv.ext_x1 <= sv.W &&
+                                  tile_y0 + pv.ext_y0 >= 0 && tile_y0 + pv.ext_y1 <= sv.H);
         int P[TPX][TG], F[TPX][TG];
         int cnt[COUNT ? TPX : 1][COUNT ? TG : 1];
         TopK<K> top[TPX];
@@ -298,36 +341,8 @@ __global__ void __launch_bounds__(TNT, 1)
             const int nt = meta.x & 0xff;
             const uint32_t lane_base = stage0 + (uint32_t)slot * STAGE_BYTES + (uint32_t)lane * PB;
             uint32_t rec = hdr_a + (uint32_t)offsetof(StageRec, img);
-            for (int k = 0; k < nt; ++k, rec += (uint32_t)sizeof(ImageRec)) {
-                const int2 ir = lds_v2<0>(rec);   // {slot_off, pitch_bytes}
-                const uint32_t bk = lane_base + (uint32_t)ir.x + (uint32_t)(warp * ir.y);
-#pragma unroll
-                for (int j4 = 0; j4 < TG / 4; ++j4) {
-                    const int4 o = (j4 == 0) ? lds_v4<16>(rec) : ((j4 == 1) ? lds_v4<32>(rec) : ((j4 == 2) ? lds_v4<48>(rec) : lds_v4<64>(rec)));
-                    static_assert(TG <= TGMAX && TGMAX == 16, "offset loads above cover 16 candidates");
-                    const int off[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int j = j4 * 4 + q;
-                        const uint32_t addr = bk + off[q];
-                        uint32_t w[TPX];
-                        w[0] = lds_u32<0>(addr);
-                        if (TPX > 1) w[TPX - 1] = lds_u32<32 * PB>(addr);
-#pragma unroll
-                        for (int h = 0; h < TPX; ++h) {
-                            P[h][j] = __dp2a_lo((int)w[h], 0x0001, P[h][j]);   // += low half  (psi, signed 16 bit)
-                            F[h][j] = __dp2a_lo((int)w[h], 0x0100, F[h][j]);   // += high half (phi)
-                            if (COUNT) {
-                                // valid <=> word != 0 (the quantiser never maps a valid pair to 0): one compare and
-                                // one predicated add in place (the compiler's select form costs a move more)
-                                asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}"
-                                    : "+r"(cnt[h][j])
-                                    : "r"(w[h]));
-                            }
-                        }
-                    }
-                }
-            }
+            if (COUNT && count_here) gather_images<TG, true, COUNT ? TPX : 1>(nt, rec, lane_base, warp, P, F, cnt);
+            else gather_images<TG, false, COUNT ? TPX : 1>(nt, rec, lane_base, warp, P, F, cnt);
             __syncwarp();
             if (lane == 0) mbar_arrive(empty);
             if (meta.x >> 8) {
@@ -364,8 +379,8 @@ __global__ void __launch_bounds__(TNT, 1)
                         P[h][j] = 0;
                         F[h][j] = 0;
                         bool alive = in_bounds[h] && (!screen || (t > 0.0f && t * t >= r));
-                        if (COUNT) {
-                            alive = alive && cnt[h][j] >= p.min_observations;   // kernels.cu:318 obs_count < min_obs
+                        if (COUNT) {   // kernels.cu:318 obs_count < min_obs (every observation valid where nothing is counted)
+                            alive = alive && (count_here ? cnt[h][j] : sv.T) >= p.min_observations;
                             cnt[h][j] = 0;
                         }
                         if (SIGMAG) {
