@@ -127,6 +127,25 @@ def merge_results(search, top_n=0):
     return n.value
 
 
+def make_banded_search(sci_imgs, var_imgs, psf_kernels, zeroed_times, candidates_vy, rank, world, num_bytes=-1,
+                       y_bounds=None):
+    """The StackSearch of one rank of a multi-GPU search: start rows ``y_bounds`` (default: the whole image) are
+    split into ``world`` contiguous bands, this rank's band becomes the search's y start bounds, and -- for float32
+    stacks -- psi/phi is built only for the image rows that band can reach with the given candidate y-velocities.
+    Returns ``(search, band)``; run ``search.search_all(candidates, True)`` and then ``merge_results(search)``."""
+    from .search import StackSearch
+    height = int(np.shape(sci_imgs[0])[0])
+    y0, y1 = (0, height) if y_bounds is None else y_bounds
+    band = row_bands(y0, y1, world)[rank]
+    rows = None
+    if num_bytes not in (1, 2) and band[0] < band[1]:   # the scale of an encoded stack depends on every row
+        rows = band_rows(band, candidates_vy, zeroed_times, height)
+    s = StackSearch(sci_imgs, var_imgs, psf_kernels, zeroed_times, num_bytes, rows=rows)
+    if band[0] < band[1]:
+        s.set_start_bounds_y(band[0], band[1])
+    return s, band
+
+
 def sharded_search(search, candidates, comm, top_n=0):
     """search_all over the full start bounds of `search`, sharded in row bands over comm.world ranks."""
     p = search.params
