@@ -82,6 +82,10 @@ struct kb_stack_s {
     bool keep_raw = false;        // enough HBM to keep d_raw for good (psi/phi curves are gathered from it)
     void *d_search = nullptr;  // canonical pitched search copy
     uint32_t *d_screen = nullptr;  // 16-bit fixed-point screening copy of the same pixels (StackView::screen)
+    // Runs of closely spaced exposures (several per night): {first image, count}.  The screening copy carries one
+    // summed plane per run after its T image planes (psi_phi.cu run_planes_kernel).
+    std::vector<int2> runs;
+    int2 *d_runs = nullptr;
     float q_step_psi = 1.0f, q_step_phi = 1.0f;  // its quantisation steps; known once the stack's value range is
     bool q_known = false;
     double *d_times = nullptr;
@@ -115,6 +119,37 @@ struct kb_stack_s {
 };
 
 static size_t pair_bytes(int nb) { return 2 * (size_t)nb; }
+static size_t screen_bytes(kb_handle h) {   // T image planes + one plane per run
+    return ((size_t)h->T + h->runs.size()) * h->H * h->Wp * sizeof(uint32_t);
+}
+
+// Consecutive images closer than this (days) form a run: 72 minutes, several exposures of one field in a night.
+static constexpr double kRunGapDays = 0.05;
+static void find_runs(kb_handle h) {
+    h->runs.clear();
+    const char *off = getenv("KB_NO_RUN_PLANES");
+    if (off && off[0] == '1') return;
+    int i = 0;
+    while (i < h->T) {
+        int j = i + 1;
+        while (j < h->T && j - i < 64 && h->times[j] - h->times[j - 1] >= 0.0 && h->times[j] - h->times[j - 1] <= kRunGapDays) ++j;
+        if (j - i >= 2) h->runs.push_back(make_int2(i, j - i));
+        i = j;
+    }
+}
+static void upload_runs(kb_handle h, cudaStream_t st) {
+    if (h->runs.empty() || h->d_runs) return;
+    KB_CUDA(cudaMalloc(&h->d_runs, sizeof(int2) * h->runs.size()));
+    KB_CUDA(cudaMemcpyAsync(h->d_runs, h->runs.data(), sizeof(int2) * h->runs.size(), cudaMemcpyHostToDevice, st));
+}
+static void build_screen_rows(kb_handle h, int r0, int nr, cudaStream_t st) {
+    launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
+                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, r0,
+                         nr, st);
+    launch_run_planes_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
+                           h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi,
+                           h->d_runs, (int)h->runs.size(), r0, nr, st);
+}
 
 static void use_device(kb_handle h) { KB_CUDA(cudaSetDevice(h->device)); }
 
@@ -136,6 +171,7 @@ static StackView make_view(kb_handle h) {
     sv.q_step_psi = h->q_step_psi;
     sv.q_step_phi = h->q_step_phi;
     sv.all_valid = h->all_valid ? 1 : 0;
+    sv.n_runs = (int)h->runs.size();
     return sv;
 }
 
@@ -319,7 +355,9 @@ static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
     cudaStream_t st = h->stream;
     h->times.assign(times, times + h->T);
     KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
-    KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
+    find_runs(h);
+    KB_CUDA(cudaMalloc(&h->d_screen, screen_bytes(h)));
+    upload_runs(h, st);
     KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, st));
     const char *nozm = getenv("KB_NO_ZERO_MARKER");
@@ -359,9 +397,7 @@ static void finish_stack(kb_handle h, float2 *d_pairs, const double *times) {
     }
     h->zero_marker = h->zm_known;
     launch_canonicalise_rows(d_ref, h->W, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0, nr, st);
-    launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
-                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, r0,
-                         nr, st);
+    build_screen_rows(h, r0, nr, st);
     KB_CUDA(cudaStreamSynchronize(st));
     if (d_ref != d_pairs) cudaFree(d_pairs);
     h->d_raw = d_ref;
@@ -454,6 +490,7 @@ static void destroy_handle(kb_handle h) {
     cudaSetDevice(h->device);
     if (h->host_thread.joinable()) h->host_thread.join();
     if (h->plan_cache) tiled_plan_destroy(h->plan_cache);
+    if (h->d_runs) cudaFree(h->d_runs);
     if (h->d_raw) cudaFree(h->d_raw);
     if (h->host_stream) cudaStreamDestroy(h->host_stream);
     free_device_stack(h);
@@ -503,9 +540,10 @@ static void upload_stack(kb_handle h) {
     const size_t rows = (size_t)h->T * h->H;
     const int r0 = h->row_lo, nr = h->row_hi - h->row_lo;   // the rows this handle holds (all of them as a rule)
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
-    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
+    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, screen_bytes(h)));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->stream));
+    upload_runs(h, h->stream);
     {
         cudaMemcpy3DParms q;
         memset(&q, 0, sizeof(q));
@@ -553,9 +591,7 @@ static void upload_stack(kb_handle h) {
                              std::max(fabsf(h->meta.phi_min_val), fabsf(h->meta.phi_max_val)));
         }
     }
-    launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
-                         h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi, r0,
-                         nr, h->stream);
+    build_screen_rows(h, r0, nr, h->stream);
     h->on_gpu = true;
 }
 
@@ -591,7 +627,7 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     if (row_hi - row_lo < 2 * UploadProgress::kMaxChunks) return false;
     const int64_t span = row_hi - row_lo;
     if (!h->d_search) KB_CUDA(cudaMalloc(&h->d_search, rows * h->Wp * pb));
-    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, rows * h->Wp * sizeof(uint32_t)));
+    if (!h->d_screen) KB_CUDA(cudaMalloc(&h->d_screen, screen_bytes(h)));
     if (!h->d_times) KB_CUDA(cudaMalloc(&h->d_times, sizeof(double) * h->T));
     UploadProgress &up = h->up;
     if (!h->copy_stream) {
@@ -607,10 +643,11 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
     KB_CUDA(cudaEventRecord(up.ready, h->stream));
     KB_CUDA(cudaStreamWaitEvent(h->copy_stream, up.ready, 0));
     KB_CUDA(cudaMemcpyAsync(h->d_times, h->times.data(), sizeof(double) * h->T, cudaMemcpyHostToDevice, h->copy_stream));
+    upload_runs(h, h->copy_stream);
     if (const char *poison = getenv("KB_POISON_STACK"))  // tests: rows that are not uploaded must never be read
         if (poison[0] == '1') {
             KB_CUDA(cudaMemsetAsync(h->d_search, 0xA5, rows * h->Wp * pb, h->copy_stream));
-            KB_CUDA(cudaMemsetAsync(h->d_screen, 0xA5, rows * h->Wp * sizeof(uint32_t), h->copy_stream));
+            KB_CUDA(cudaMemsetAsync(h->d_screen, 0xA5, screen_bytes(h), h->copy_stream));
         }
     h->zero_marker = (h->nb == 4) ? h->zm_known : 0;
     up.n_chunks = UploadProgress::kMaxChunks;
@@ -627,9 +664,7 @@ static bool upload_stack_pipelined(kb_handle h, int row_lo, int row_hi, uint64_t
         KB_CUDA(cudaMemcpy3DAsync(&q, h->copy_stream));
         launch_canonicalise_rows(h->d_search, h->Wp, h->d_search, h->T, h->H, h->W, h->Wp, h->nb, h->zero_marker, r0,
                                  r1 - r0, h->copy_stream);
-        launch_quantise_rows(h->d_search, h->d_screen, h->T, h->H, h->Wp, h->nb, h->zero_marker, h->meta.psi_scale,
-                             h->meta.psi_min_val, h->meta.phi_scale, h->meta.phi_min_val, h->q_step_psi, h->q_step_phi,
-                             r0, r1 - r0, h->copy_stream);
+        build_screen_rows(h, r0, r1 - r0, h->copy_stream);
         up.row_end[c] = r1;
         KB_CUDA(cudaEventRecord(up.ev[c], h->copy_stream));
     }
@@ -1071,7 +1106,7 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
         } else {
             if (h->plan_cache) tiled_plan_destroy(h->plan_cache);
             h->plan_cache = nullptr;
-            plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data());
+            plan = tiled_plan_create(sv, p, vx, vy, n_cand, st, &why, h->times.data(), h->runs.data());
             if (plan) {
                 h->plan_cache = plan;
                 h->plan_vx.assign(vx, vx + n_cand);

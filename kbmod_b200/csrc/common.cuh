@@ -63,6 +63,7 @@ struct StackView {
     const uint32_t *screen;
     float q_step_psi, q_step_phi;
     int all_valid;   // 1 = no invalid pair anywhere in the rows this stack holds (known from the constructor's scan)
+    int n_runs;      // run planes that follow the T image planes of `screen` (psi_phi.cu run_planes_kernel)
 };
 
 // Per-pixel result slot written by the search kernels: 16 bytes, [pixel][K].
@@ -124,8 +125,10 @@ int merge_clip_survivors(const ClipSurvivor *d_surv, uint64_t n, Slot *d_slots, 
 struct TiledPlan;  // opaque: schedule for the TMA-staged kernel
 // Returns nullptr (and a reason) when the tiled kernel cannot be used for this search.
 // h_times: host copy of the T image times (avoids a device read-back while an upload is in flight).
+// h_runs: the runs of closely spaced exposures the screening copy has planes for ({first image, count}, sv.n_runs).
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
-                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times = nullptr);
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times = nullptr,
+                             const int2 *h_runs = nullptr);
 // A stack upload in flight on another stream: rows [0, row_end[c]) of every image are on the device (and
 // canonical) once ev[c] has fired.  With it, launch_search_tiled starts on the rows that have arrived: the frame is
 // searched in row bands, each waiting only for the chunk that completes its reach.
@@ -171,6 +174,11 @@ int launch_quantise_rows(const void *d_search, uint32_t *d_screen, int T, int H,
                          float psi_scale, float psi_min, float phi_scale, float phi_min, float step_psi,
                          float step_phi, int r0, int nr, cudaStream_t st);
 int launch_minmax_pitched(const void *d_search, uint64_t n_pairs, uint32_t *d_mm, cudaStream_t st);
+// Run planes of the screening copy (planes T .. T + n_runs - 1): per pixel the quantised sum over the images of a run
+// of closely spaced exposures; d_runs[c] = {first image, number of images}.
+int launch_run_planes_rows(const void *d_search, uint32_t *d_screen, int T, int H, int Wp, int nb, int zero_marker,
+                           float psi_scale, float psi_min, float phi_scale, float phi_min, float step_psi, float step_phi,
+                           const int2 *d_runs, int n_runs, int r0, int nr, cudaStream_t st);
 // float stacks: sets *d_flag to 1 when some valid pair is exactly (0, 0) (then the zero marker cannot be used).
 int launch_detect_valid_zero_pairs(const void *d_src, int src_pitch, int T, int H, int W, uint32_t *d_flag,
                                    cudaStream_t st);

@@ -463,6 +463,85 @@ int launch_quantise_rows(const void *d_search, uint32_t *d_screen, int T, int H,
     return 1;
 }
 
+// ---- run planes of the screening copy -----------------------------------------------------------------------------------
+// Exposures taken minutes apart (several per night) put a slow mover on the same pixel, so a candidate's gathers for
+// such a run of images read one pixel position in each of them.  For every run the screening copy carries one more
+// plane: per pixel the sum of the run's valid values, quantised with m times the step (m = images in the run), so
+// that  m * q_run * step  stands for the m single words with the same error bound (<= 0.502 m step; a pixel with data
+// in the run never maps to the word 0).  The search kernel adds  m * q_run  with one IDP.2A whose byte multiplier
+// is m, wherever all candidates of a group keep their pixel offsets through the run.
+template <int NB>
+__device__ __forceinline__ bool decoded_pair(const void *src, uint64_t g, int zero_marker, float psi_scale, float psi_min,
+                                             float phi_scale, float phi_min, float &a, float &b) {
+    if (NB == 4) {
+        const float2 v = reinterpret_cast<const float2 *>(src)[g];
+        a = v.x;
+        b = v.y;
+        return zero_marker ? (((__float_as_uint(a) | __float_as_uint(b)) << 1) != 0u) : (b == b);
+    } else if (NB == 2) {
+        const ushort2 v = reinterpret_cast<const ushort2 *>(src)[g];
+        if (v.x == 0) return false;  // canonical: both or none
+        a = (float)__dadd_rn(__dmul_rn((double)v.x - 1.0, (double)psi_scale), (double)psi_min);
+        b = (float)__dadd_rn(__dmul_rn((double)v.y - 1.0, (double)phi_scale), (double)phi_min);
+        return true;
+    } else {
+        const uchar2 v = reinterpret_cast<const uchar2 *>(src)[g];
+        if (v.x == 0) return false;
+        a = (float)__dadd_rn(__dmul_rn((double)v.x - 1.0, (double)psi_scale), (double)psi_min);
+        b = (float)__dadd_rn(__dmul_rn((double)v.y - 1.0, (double)phi_scale), (double)phi_min);
+        return true;
+    }
+}
+
+template <int NB>
+__global__ void run_planes_kernel(const void *__restrict__ src, uint32_t *__restrict__ screen, int T, int H, int r0, int nr,
+                                  int Wp, int zero_marker, float psi_scale, float psi_min, float phi_scale, float phi_min,
+                                  float step_psi, float step_phi, const int2 *__restrict__ runs, int n_runs) {
+    const uint64_t per_run = (uint64_t)nr * (uint64_t)Wp, total = per_run * (uint64_t)n_runs;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i / per_run);
+        const uint64_t in_img = (uint64_t)r0 * Wp + i % per_run;   // (row, column) offset inside an image
+        const int2 run = runs[c];                                   // {first image, number of images}
+        double sa = 0.0, sb = 0.0;
+        bool any = false;
+        for (int k = 0; k < run.y; ++k) {
+            float a, b;
+            if (decoded_pair<NB>(src, (uint64_t)(run.x + k) * H * Wp + in_img, zero_marker, psi_scale, psi_min, phi_scale,
+                                 phi_min, a, b)) {
+                sa += (double)a;
+                sb += (double)b;
+                any = true;
+            }
+        }
+        uint32_t w = 0u;
+        if (any) {
+            const double m = (double)run.y;
+            int qa = __double2int_rn(sa / (m * (double)step_psi)), qb = __double2int_rn(sb / (m * (double)step_phi));
+            qa = max(-32767, min(32767, qa));
+            qb = max(-32767, min(32767, qb));
+            if (qa == 0 && qb == 0) qb = 1;
+            w = ((uint32_t)qa & 0xffffu) | ((uint32_t)qb << 16);
+        }
+        screen[(uint64_t)(T + c) * H * Wp + in_img] = w;
+    }
+}
+
+int launch_run_planes_rows(const void *d_search, uint32_t *d_screen, int T, int H, int Wp, int nb, int zero_marker,
+                           float psi_scale, float psi_min, float phi_scale, float phi_min, float step_psi, float step_phi,
+                           const int2 *d_runs, int n_runs, int r0, int nr, cudaStream_t st) {
+    if (nr <= 0 || n_runs <= 0) return 0;
+#define KB_RUNS(NBV)                                                                                                   \
+    run_planes_kernel<NBV><<<148 * 8, 256, 0, st>>>(d_search, d_screen, T, H, r0, nr, Wp, zero_marker, psi_scale, psi_min, \
+                                                    phi_scale, phi_min, step_psi, step_phi, d_runs, n_runs)
+    if (nb == 4) KB_RUNS(4);
+    else if (nb == 2) KB_RUNS(2);
+    else KB_RUNS(1);
+#undef KB_RUNS
+    KB_CUDA(cudaGetLastError());
+    return 1;
+}
+
 // max |psi| and max |phi| over the valid pairs of a canonical float search copy (padding and invalid pairs are NaN
 // or zero and do not matter): d_mm = {psi_min, psi_max, phi_min, phi_max} as ordered uints, like launch_minmax.
 int launch_minmax_pitched(const void *d_search, uint64_t n_pairs, uint32_t *d_mm, cudaStream_t st) {

@@ -88,7 +88,8 @@ static void screen_bounds(int T, float step_psi, float step_phi, float &e_psi, f
 }
 
 TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const float *h_vx, const float *h_vy,
-                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times) {
+                             uint64_t n_cand, cudaStream_t st, std::string *why_not, const double *h_times,
+                             const int2 *h_runs) {
     auto no = [&](const char *why) -> TiledPlan * {
         if (why_not) *why_not = why;
         return nullptr;
@@ -217,81 +218,120 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int rmax = (TBY + max_sy + TCH - 1) / TCH * TCH;
     const int max_ch = rmax / TCH;
 
-    // ---- stage records, group by group (greedy packing of consecutive images into <= STAGE_BYTES) ---------------
+    // ---- stage records, group by group (greedy packing of consecutive records into <= STAGE_BYTES) ---------------
+    // A record is one image -- or, with `use_runs`, a whole run of closely spaced exposures through which every
+    // candidate of the group keeps its pixel offsets: the gather then reads the run's summed plane of the screening
+    // copy once, with the run's length as the multiplier of its IDP.2A.
     std::vector<int> group_reach(std::max(n_groups, 1), 0);
     std::vector<int4> group_ext(std::max(n_groups, 1), make_int4(INT_MAX, INT_MIN, INT_MAX, INT_MIN));
-    std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
     std::vector<int> cand((size_t)std::max(n_groups, 1) * TG, -1);
-    bool overflow = false;
-#pragma omp parallel for schedule(dynamic, 8)
-    for (int g = 0; g < n_groups; ++g) {
-        const int b = group_start[g], n = group_start[g + 1] - b;
-        int dx[TGMAX], dy[TGMAX];
-        for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
-        std::vector<StageRec> &out = per_group[g];
-        StageRec cur;
-        memset(&cur, 0, sizeof(cur));
-        int nt = 0, used = 0, tx = 0, t0 = 0;
-        auto flush = [&](bool last) {
-            cur.meta = make_int4(nt | ((last ? 1 : 0) << 8), g, t0, tx + (int)sizeof(StageRec));
-            out.push_back(cur);
+    std::vector<int> run_at(T, -1);   // index of the run that starts at image t
+    for (int c = 0; c < sv.n_runs && h_runs; ++c) run_at[h_runs[c].x] = c;
+    long long n_records[2] = {0, 0};
+    auto build = [&](bool use_runs, std::vector<StageRec> &stages) -> const char * {
+        std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
+        bool overflow = false;
+        long long records = 0;
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : records)
+        for (int g = 0; g < n_groups; ++g) {
+            const int b = group_start[g], n = group_start[g + 1] - b;
+            int dx[TGMAX], dy[TGMAX];
+            for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
+            std::vector<StageRec> &out = per_group[g];
+            StageRec cur;
             memset(&cur, 0, sizeof(cur));
-            nt = used = tx = 0;
-        };
-        for (int t = 0; t < T; ++t) {
-            int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
-            for (int j = 0; j < n; ++j) {
-                const int c = tabulated[b + j];
-                tab_offset(h_vx[c], times[t], dx[j]);
-                tab_offset(h_vy[c], times[t], dy[j]);
-                mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
-                mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
+            int nt = 0, used = 0, tx = 0, t0 = 0;
+            auto flush = [&](bool last) {
+                cur.meta = make_int4(nt | ((last ? 1 : 0) << 8), g, t0, tx + (int)sizeof(StageRec));
+                out.push_back(cur);
+                memset(&cur, 0, sizeof(cur));
+                nt = used = tx = 0;
+            };
+            for (int t = 0; t < T;) {
+                int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+                for (int j = 0; j < n; ++j) {
+                    const int c = tabulated[b + j];
+                    tab_offset(h_vx[c], times[t], dx[j]);
+                    tab_offset(h_vy[c], times[t], dy[j]);
+                    mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
+                    mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
+                }
+                int plane = t, mult = 1;
+                if (use_runs && run_at[t] >= 0) {   // do all candidates stay on their pixels through the run?
+                    const int m = h_runs[run_at[t]].y;
+                    bool same = true;
+                    for (int k = 1; k < m && same; ++k)
+                        for (int j = 0; j < n && same; ++j) {
+                            const int c = tabulated[b + j];
+                            int ox, oy;
+                            tab_offset(h_vx[c], times[t + k], ox);
+                            tab_offset(h_vy[c], times[t + k], oy);
+                            same = ox == dx[j] && oy == dy[j];
+                        }
+                    if (same) {
+                        plane = T + run_at[t];
+                        mult = m;
+                    }
+                }
+                mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
+                const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
+                const int widx = std::max(0, (need_w - w_base + w_step - 1) / w_step);
+                const int pitch = w_base + w_step * widx;
+                const int rows_pad = (nrows + TCH - 1) / TCH * TCH;
+                const int bytes = rows_pad * pitch * PB;
+                if (pitch > w_max || widx >= NMAPS || nrows > rmax || nrows > 255 || bytes > STAGE_BYTES) {
+                    overflow = true;
+                    break;
+                }
+                if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
+                if (nt == 0) t0 = t;
+                cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 8) | (plane << 12), used);
+                group_reach[g] = std::max(group_reach[g], mny + rows_pad);
+                group_ext[g].x = std::min(group_ext[g].x, mnx);
+                group_ext[g].y = std::max(group_ext[g].y, mnx + pitch);
+                group_ext[g].z = std::min(group_ext[g].z, mny);
+                group_ext[g].w = std::max(group_ext[g].w, mny + rows_pad);
+                cur.img[nt].slot_off = used;
+                cur.img[nt].pitch_bytes = pitch * PB;
+                cur.img[nt].mult_lo = mult;         // byte 0: multiplies the low half of the word (psi)
+                cur.img[nt].mult_hi = mult << 8;    // byte 1: multiplies the high half (phi)
+                for (int j = 0; j < TGMAX; ++j)
+                    cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
+                used += bytes;
+                tx += bytes;
+                ++nt;
+                ++records;
+                t += mult;
             }
-            mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
-            const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
-            const int widx = std::max(0, (need_w - w_base + w_step - 1) / w_step);
-            const int pitch = w_base + w_step * widx;
-            const int rows_pad = (nrows + TCH - 1) / TCH * TCH;
-            const int bytes = rows_pad * pitch * PB;
-            if (pitch > w_max || widx >= NMAPS || nrows > rmax || bytes > STAGE_BYTES) {
-                overflow = true;
-                break;
-            }
-            if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
-            if (nt == 0) t0 = t;
-            cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 16), used);
-            group_reach[g] = std::max(group_reach[g], mny + rows_pad);
-            group_ext[g].x = std::min(group_ext[g].x, mnx);
-            group_ext[g].y = std::max(group_ext[g].y, mnx + pitch);
-            group_ext[g].z = std::min(group_ext[g].z, mny);
-            group_ext[g].w = std::max(group_ext[g].w, mny + rows_pad);
-            cur.img[nt].slot_off = used;
-            cur.img[nt].pitch_bytes = pitch * PB;
-            for (int j = 0; j < TGMAX; ++j)
-                cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
-            used += bytes;
-            tx += bytes;
-            ++nt;
+            if (nt > 0) flush(true);
         }
-        if (nt > 0) flush(true);
-    }
-    if (overflow) return no("velocity spread too large for a shared-memory stage");
-    std::vector<StageRec> stages;
-    {
+        n_records[use_runs ? 1 : 0] = records;
+        if (overflow) return "velocity spread too large for a shared-memory stage";
         size_t total = 0;
         for (auto &v : per_group) total += v.size();
-        if (total >= (1ull << 31)) return no("too many stages");
+        if (total >= (1ull << 31)) return "too many stages";
         stages.reserve(std::max<size_t>(total, 1));
         for (auto &v : per_group) {
             stages.insert(stages.end(), v.begin(), v.end());
             std::vector<StageRec>().swap(v);
         }
-    }
+        return nullptr;
+    };
+    // The schedule every tile uses -- with run records where the stack has runs -- and, for searches that count
+    // observations, a second one of single images for the tiles that have to count (a run's summed word cannot say
+    // how many of its images had data).
+    const bool have_runs = sv.n_runs > 0 && h_runs != nullptr;
+    const bool counting = !p.do_sigmag_filter && p.min_observations > 0;
+    std::vector<StageRec> stages, stages_plain;
+    if (const char *err = build(have_runs, stages)) return no(err);
+    if (have_runs && counting)
+        if (const char *err = build(false, stages_plain)) return no(err);
     const int n_stages = (int)stages.size();
     if (getenv("KB_DEBUG"))
-        fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d stages=%d max_sx=%d max_sy=%d "
-                "w_base=%d w_step=%d rmax=%d sx_lim=%d sy_lim=%d\n", N, NTab, exact.size(), n_groups, n_stages,
-                max_sx, max_sy, w_base, w_step, rmax, sx_lim, sy_lim);
+        fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d stages=%d (+%zu single-image) "
+                "records=%lld of %lld max_sx=%d max_sy=%d w_base=%d w_step=%d rmax=%d sx_lim=%d sy_lim=%d\n", N, NTab,
+                exact.size(), n_groups, n_stages, stages_plain.size(), have_runs ? n_records[1] : n_records[0],
+                (long long)n_groups * T, max_sx, max_sy, w_base, w_step, rmax, sx_lim, sy_lim);
 
     std::unique_ptr<TiledPlan> plan(new TiledPlan());
     plan->nb = sv.nb;
@@ -300,11 +340,15 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     plan->tg = TG;
     auto up = [](size_t b) { return (b + 255) / 256 * 256; };
     const size_t b_st = up(std::max<size_t>(stages.size(), 1) * sizeof(StageRec)), b_cand = up(cand.size() * 4),
-                 b_ex = up(std::max<size_t>(exact.size(), 1) * 4);
-    KB_CUDA(cudaMalloc(&plan->d_block, b_st + b_cand + b_ex));
+                 b_ex = up(std::max<size_t>(exact.size(), 1) * 4),
+                 b_pl = stages_plain.empty() ? 0 : up(stages_plain.size() * sizeof(StageRec));
+    KB_CUDA(cudaMalloc(&plan->d_block, b_st + b_cand + b_ex + b_pl));
     uint8_t *d = (uint8_t *)plan->d_block;
     if (!stages.empty())
         KB_CUDA(cudaMemcpyAsync(d, stages.data(), stages.size() * sizeof(StageRec), cudaMemcpyHostToDevice, st));
+    if (!stages_plain.empty())
+        KB_CUDA(cudaMemcpyAsync(d + b_st + b_cand + b_ex, stages_plain.data(), stages_plain.size() * sizeof(StageRec),
+                                cudaMemcpyHostToDevice, st));
     KB_CUDA(cudaMemcpyAsync(d + b_st, cand.data(), cand.size() * 4, cudaMemcpyHostToDevice, st));
     if (!exact.empty())
         KB_CUDA(cudaMemcpyAsync(d + b_st + b_cand, exact.data(), exact.size() * 4, cudaMemcpyHostToDevice, st));
@@ -316,6 +360,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     v.n_exact = (int)exact.size();
     v.n_groups = n_groups;
     v.n_stages = n_stages;
+    v.stages_plain = stages_plain.empty() ? v.stages : (const StageRec *)(d + b_st + b_cand + b_ex);
+    v.n_stages_plain = stages_plain.empty() ? n_stages : (int)stages_plain.size();
     v.w_base = w_base;
     v.w_step = w_step;
     v.max_ch = max_ch;
@@ -352,7 +398,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
 
     // ---- tensor maps over the screening copy: dims (pixels, rows, images) of 32-bit words, one per box width; what
     // lies outside the image is filled with zeros by the TMA unit == the screening copy's "no data" word
-    const cuuint64_t gdim[3] = {(cuuint64_t)sv.W, (cuuint64_t)sv.H, (cuuint64_t)sv.T};
+    const cuuint64_t gdim[3] = {(cuuint64_t)sv.W, (cuuint64_t)sv.H, (cuuint64_t)(sv.T + sv.n_runs)};
     const cuuint64_t gstr[2] = {(cuuint64_t)sv.Wp * PB, (cuuint64_t)sv.Wp * PB * sv.H};
     const cuuint32_t estr[3] = {1, 1, 1};
     for (int i = 0; i < NMAPS; ++i) {

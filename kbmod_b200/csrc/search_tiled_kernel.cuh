@@ -44,11 +44,13 @@ static constexpr int kScreenPairBytes = 4;  // one 32-bit word of the screening 
 
 // One pipeline stage as the host lays it out (and as it lands in shared memory by one bulk copy):
 //   meta   {nt | last << 8, group, t0, tx_bytes}
-//   box[k] {ox, oy, nrows | widx << 16, slot_off}   for the nt images of the stage (k < TMAXTC): the producer's view
+//   box[k] {ox, oy, nrows | widx << 8 | plane << 12, slot_off}   for the nt records of the stage (k < TMAXTC): the
+//          producer's view; plane = image index, or T + run index for a run's summed plane
 //   img[k] what a consumer needs for image k: where its box starts in the stage, the box's row pitch in bytes, and
 //          offs[j], the byte offset of candidate j's pixel inside the box relative to the thread's own pixel
 struct ImageRec {
-    int slot_off, pitch_bytes, pad[2];
+    int slot_off, pitch_bytes;
+    int mult_lo, mult_hi;   // IDP.2A multipliers of the record: m and m << 8, m = images the record stands for
     int offs[TGMAX];
 };
 struct StageRec {
@@ -66,6 +68,8 @@ struct TmapSet {
 
 struct PlanView {
     const StageRec *stages;  // [n_stages]
+    const StageRec *stages_plain;  // schedule of single images (== stages unless the stack has run planes and the search
+    int n_stages_plain;            // counts observations): used by the tiles that have to count
     const int *cand;         // [n_groups][group size]  candidate index or -1
     const int *exact;        // candidates evaluated by the exact routine
     int n_exact, n_groups, n_stages, w_base, w_step, max_ch, T;
@@ -180,7 +184,7 @@ __device__ __forceinline__ void gather_images(int nt, uint32_t rec, uint32_t lan
                                               int (&F)[TPX][TG], int (&cnt)[CT][CT == 1 ? 1 : TG]) {
     constexpr int PB = kScreenPairBytes;
     for (int k = 0; k < nt; ++k, rec += (uint32_t)sizeof(ImageRec)) {
-        const int2 ir = lds_v2<0>(rec);   // {slot_off, pitch_bytes}
+        const int4 ir = lds_v4<0>(rec);   // {slot_off, pitch_bytes, multiplier for psi, multiplier for phi}
         const uint32_t bk = lane_base + (uint32_t)ir.x + (uint32_t)(warp * ir.y);
 #pragma unroll
         for (int j4 = 0; j4 < TG / 4; ++j4) {
@@ -196,8 +200,8 @@ __device__ __forceinline__ void gather_images(int nt, uint32_t rec, uint32_t lan
                 if (TPX > 1) w[TPX - 1] = lds_u32<32 * PB>(addr);
 #pragma unroll
                 for (int h = 0; h < TPX; ++h) {
-                    P[h][j] = __dp2a_lo((int)w[h], 0x0001, P[h][j]);   // += low half  (psi, signed 16 bit)
-                    F[h][j] = __dp2a_lo((int)w[h], 0x0100, F[h][j]);   // += high half (phi)
+                    P[h][j] = __dp2a_lo((int)w[h], ir.z, P[h][j]);   // += m * low half  (psi, signed 16 bit)
+                    F[h][j] = __dp2a_lo((int)w[h], ir.w, F[h][j]);   // += m * high half (phi)
                     if (DO_COUNT) {
                         asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}"
                             : "+r"(cnt[h][j])
@@ -255,9 +259,15 @@ __global__ void __launch_bounds__(TNT, 1)
 
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
-    const int n_stages = pv.n_stages;
     constexpr int PB = kScreenPairBytes;
     constexpr int TG = group_size(SIGMAG);
+    // Observations only have to be counted where some can be invalid: a stack with invalid pixels, or a tile from
+    // which some box of the schedule reaches over the image's edge (CTA-uniform).  Tiles that count follow the
+    // schedule of single images (a run's summed word cannot say how many of its images had data).
+    const bool count_here = COUNT && !(sv.all_valid && tile_x0 + pv.ext_x0 >= 0 && tile_x0 + pv.ext_x1 <= sv.W &&
+                                       tile_y0 + pv.ext_y0 >= 0 && tile_y0 + pv.ext_y1 <= sv.H);
+    const StageRec *const stage_list = count_here ? pv.stages_plain : pv.stages;
+    const int n_stages = count_here ? pv.n_stages_plain : pv.n_stages;
 
     if (warp == TBY) {
         // ===================== producer warp: TMA box loads + the stage record =================================
@@ -265,7 +275,7 @@ __global__ void __launch_bounds__(TNT, 1)
         // so the global-memory latency overlaps the wait for a free slot; fields are handed out by shuffles.
         const unsigned FULLM = 0xffffffffu;
         auto fetch = [&](int s) -> int4 {
-            if (lane < 1 + TMAXTC && s < n_stages) return __ldg(reinterpret_cast<const int4 *>(pv.stages + s) + lane);
+            if (lane < 1 + TMAXTC && s < n_stages) return __ldg(reinterpret_cast<const int4 *>(stage_list + s) + lane);
             return make_int4(0, 0, 0, 0);
         };
         int4 nxt = fetch(0);
@@ -275,7 +285,7 @@ __global__ void __launch_bounds__(TNT, 1)
             const int4 cur = nxt;
             nxt = fetch(s + 1);
             if (s >= TS) mbar_wait(empty, ((s / TS) - 1) & 1);
-            const int nt = __shfl_sync(FULLM, cur.x, 0) & 0xff, t0 = __shfl_sync(FULLM, cur.z, 0);
+            const int nt = __shfl_sync(FULLM, cur.x, 0) & 0xff;
             const int tx = __shfl_sync(FULLM, cur.w, 0);
             if (lane == 0) mbar_arrive_expect_tx(full, (uint32_t)tx);
             __syncwarp();
@@ -286,15 +296,15 @@ __global__ void __launch_bounds__(TNT, 1)
                 const int k = min(i / pv.max_ch, TMAXTC - 1), ch = i % pv.max_ch;
                 const int bxx = __shfl_sync(FULLM, cur.x, k + 1), bxy = __shfl_sync(FULLM, cur.y, k + 1);
                 const int bxz = __shfl_sync(FULLM, cur.z, k + 1), bxw = __shfl_sync(FULLM, cur.w, k + 1);
-                const int nrows = bxz & 0xffff, widx = bxz >> 16;
+                const int nrows = bxz & 0xff, widx = (bxz >> 8) & 0xf, plane = bxz >> 12;
                 if (i < total && ch * TCH < nrows) {
                     const int pitch = pv.w_base + pv.w_step * widx;
                     tma_load_3d(stage_base + bxw + ch * TCH * pitch * PB, &maps.m[widx], tile_x0 + bxx,
-                                tile_y0 + bxy + ch * TCH, t0 + k, full);
+                                tile_y0 + bxy + ch * TCH, plane, full);
                 }
             }
             if (lane == 0)
-                bulk_load(smem_u32(s_hdr + (size_t)slot * HDR_BYTES), pv.stages + s, (uint32_t)sizeof(StageRec), full);
+                bulk_load(smem_u32(s_hdr + (size_t)slot * HDR_BYTES), stage_list + s, (uint32_t)sizeof(StageRec), full);
         }
     } else {
         // ===================== consumer warps: gather, reduce, rank ========================================
@@ -311,10 +321,6 @@ __global__ void __launch_bounds__(TNT, 1)
             pixel_index[h] = pv.pixel_base + (unsigned)((py - p.y_start_min) * sw + (px[h] - p.x_start_min));
         }
         const uint32_t hdr0 = smem_u32(s_hdr), stage0 = smem_u32(s_stage);
-        // Observations only have to be counted where some can be invalid: a stack with invalid pixels, or a tile from
-        // which some box of the schedule reaches over the image's edge (CTA-uniform).
-        const bool count_here = !(sv.all_valid && tile_x0 + pv.ext_x0 >= 0 && tile_x0 + pv.ext_x1 <= sv.W &&
-                                  tile_y0 + pv.ext_y0 >= 0 && tile_y0 + pv.ext_y1 <= sv.H);
         int P[TPX][TG], F[TPX][TG];
         int cnt[COUNT ? TPX : 1][COUNT ? TG : 1];
         TopK<K> top[TPX];
@@ -341,7 +347,7 @@ __global__ void __launch_bounds__(TNT, 1)
             const int nt = meta.x & 0xff;
             const uint32_t lane_base = stage0 + (uint32_t)slot * STAGE_BYTES + (uint32_t)lane * PB;
             uint32_t rec = hdr_a + (uint32_t)offsetof(StageRec, img);
-            if (COUNT && count_here) gather_images<TG, true, COUNT ? TPX : 1>(nt, rec, lane_base, warp, P, F, cnt);
+            if (count_here) gather_images<TG, true, COUNT ? TPX : 1>(nt, rec, lane_base, warp, P, F, cnt);
             else gather_images<TG, false, COUNT ? TPX : 1>(nt, rec, lane_base, warp, P, F, cnt);
             __syncwarp();
             if (lane == 0) mbar_arrive(empty);
