@@ -129,12 +129,32 @@ static void find_runs(kb_handle h) {
     h->runs.clear();
     const char *off = getenv("KB_NO_RUN_PLANES");
     if (off && off[0] == '1') return;
+    // Every maximal run of closely spaced exposures, and its aligned halves, quarters, ... down to pairs: a group of
+    // candidates that does not hold its pixels through a whole night often does through half of it.  Longest first
+    // at every start image (the schedule takes the first that fits).
     int i = 0;
     while (i < h->T) {
         int j = i + 1;
         while (j < h->T && j - i < 64 && h->times[j] - h->times[j - 1] >= 0.0 && h->times[j] - h->times[j - 1] <= kRunGapDays) ++j;
-        if (j - i >= 2) h->runs.push_back(make_int2(i, j - i));
+        const int m = j - i;
+        if (m >= 2) {
+            h->runs.push_back(make_int2(i, m));
+            int len = 1;
+            while (len * 2 < m) len *= 2;           // largest power of two below m
+            for (; len >= 2; len /= 2)
+                for (int s0 = i; s0 + len <= j; s0 += len) h->runs.push_back(make_int2(s0, len));
+        }
         i = j;
+    }
+    // keep the extra planes within a quarter of the image planes' footprint times four (they are a speed-up only)
+    size_t free_b = 0, total_b = 0;
+    const size_t plane = (size_t)h->H * h->Wp * sizeof(uint32_t);
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && h->runs.size() * plane > free_b / 8) {
+        std::vector<int2> whole;
+        for (const int2 &r : h->runs)   // drop the sub-runs, keep the maximal runs
+            if (whole.empty() || r.x >= whole.back().x + whole.back().y) whole.push_back(r);
+        h->runs.swap(whole);
+        if (h->runs.size() * plane > free_b / 8) h->runs.clear();
     }
 }
 static void upload_runs(kb_handle h, cudaStream_t st) {

@@ -225,8 +225,11 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     std::vector<int> group_reach(std::max(n_groups, 1), 0);
     std::vector<int4> group_ext(std::max(n_groups, 1), make_int4(INT_MAX, INT_MIN, INT_MAX, INT_MIN));
     std::vector<int> cand((size_t)std::max(n_groups, 1) * TG, -1);
-    std::vector<int> run_at(T, -1);   // index of the run that starts at image t
-    for (int c = 0; c < sv.n_runs && h_runs; ++c) run_at[h_runs[c].x] = c;
+    // runs that start at image t, longest first (the handle lists a maximal run before its halves, quarters, ...)
+    std::vector<std::vector<int>> run_at(T);
+    for (int c = 0; c < sv.n_runs && h_runs; ++c) run_at[h_runs[c].x].push_back(c);
+    for (auto &v : run_at)
+        std::stable_sort(v.begin(), v.end(), [&](int a, int b2) { return h_runs[a].y > h_runs[b2].y; });
     long long n_records[2] = {0, 0};
     auto build = [&](bool use_runs, std::vector<StageRec> &stages) -> const char * {
         std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
@@ -257,21 +260,28 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
                     mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
                 }
                 int plane = t, mult = 1;
-                if (use_runs && run_at[t] >= 0) {   // do all candidates stay on their pixels through the run?
-                    const int m = h_runs[run_at[t]].y;
-                    bool same = true;
-                    for (int k = 1; k < m && same; ++k)
+                if (use_runs && !run_at[t].empty()) {
+                    // how many images from t on do all candidates stay on their pixels?  the longest run that
+                    // starts here and fits is read as one record
+                    const int longest = h_runs[run_at[t][0]].y;
+                    int hold = 1;
+                    for (; hold < longest; ++hold) {
+                        bool same = true;
                         for (int j = 0; j < n && same; ++j) {
                             const int c = tabulated[b + j];
                             int ox, oy;
-                            tab_offset(h_vx[c], times[t + k], ox);
-                            tab_offset(h_vy[c], times[t + k], oy);
+                            tab_offset(h_vx[c], times[t + hold], ox);
+                            tab_offset(h_vy[c], times[t + hold], oy);
                             same = ox == dx[j] && oy == dy[j];
                         }
-                    if (same) {
-                        plane = T + run_at[t];
-                        mult = m;
+                        if (!same) break;
                     }
+                    for (int r : run_at[t])
+                        if (h_runs[r].y <= hold) {
+                            plane = T + r;
+                            mult = h_runs[r].y;
+                            break;
+                        }
                 }
                 mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
                 const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
@@ -318,13 +328,13 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
         return nullptr;
     };
     // The schedule every tile uses -- with run records where the stack has runs -- and, for searches that count
-    // observations, a second one of single images for the tiles that have to count (a run's summed word cannot say
-    // how many of its images had data).
+    // observations in a stack with invalid pixels, a second one of single images for the tiles that count (a run's
+    // summed word cannot say how many of its images had data; without invalid pixels it is all or none of them).
     const bool have_runs = sv.n_runs > 0 && h_runs != nullptr;
     const bool counting = !p.do_sigmag_filter && p.min_observations > 0;
     std::vector<StageRec> stages, stages_plain;
     if (const char *err = build(have_runs, stages)) return no(err);
-    if (have_runs && counting)
+    if (have_runs && counting && !sv.all_valid)
         if (const char *err = build(false, stages_plain)) return no(err);
     const int n_stages = (int)stages.size();
     if (getenv("KB_DEBUG"))
@@ -362,6 +372,8 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     v.n_stages = n_stages;
     v.stages_plain = stages_plain.empty() ? v.stages : (const StageRec *)(d + b_st + b_cand + b_ex);
     v.n_stages_plain = stages_plain.empty() ? n_stages : (int)stages_plain.size();
+    v.tile_order = nullptr;
+    plan->order_tiles = counting;   // tiles that count are slower: launched first (launch_tiled_any)
     v.w_base = w_base;
     v.w_step = w_step;
     v.max_ch = max_ch;
@@ -422,15 +434,44 @@ float tiled_plan_kernel_ms(TiledPlan *plan) { return plan ? plan->ms_accum : 0.0
 void tiled_plan_destroy(TiledPlan *plan) {
     if (!plan) return;
     if (plan->d_block) cudaFree(plan->d_block);
+    if (plan->d_order) cudaFree(plan->d_order);
     if (plan->ev0) cudaEventDestroy(plan->ev0);
     if (plan->ev1) cudaEventDestroy(plan->ev1);
     delete plan;
 }
 
 static void launch_tiled_any(TiledPlan *plan, const StackView &sv, const kb_params &p, const float *d_vx,
-                             const float *d_vy, Slot *d_slots, cudaStream_t st) {
+                             const float *d_vy, Slot *d_slots, cudaStream_t st, bool may_order) {
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     dim3 grid((sw + TBX - 1) / TBX, (sh + TBY - 1) / TBY);
+    plan->v.tile_order = nullptr;
+    if (may_order && plan->order_tiles && sv.all_valid) {   // (with invalid pixels every tile counts)
+        // Tiles from which a box reaches over the image's edge count observations and follow the single-image
+        // schedule, several times longer than the run schedule of the interior tiles: start them first, so the
+        // short tiles fill in behind them instead of the long ones forming the tail of the launch.
+        const PlanView &v = plan->v;
+        const size_t n_tiles = (size_t)grid.x * grid.y;
+        std::vector<uint2> slow, fast;
+        for (unsigned ty = 0; ty < grid.y; ++ty)
+            for (unsigned tx = 0; tx < grid.x; ++tx) {
+                const int x0 = p.x_start_min + (int)tx * TBX, y0 = p.y_start_min + (int)ty * TBY;
+                const bool inside = x0 + v.ext_x0 >= 0 && x0 + v.ext_x1 <= sv.W && y0 + v.ext_y0 >= 0 && y0 + v.ext_y1 <= sv.H;
+                (inside ? fast : slow).push_back(make_uint2(tx, ty));
+            }
+        if (!slow.empty() && !fast.empty()) {
+            slow.insert(slow.end(), fast.begin(), fast.end());
+            if (plan->order_cap < n_tiles) {
+                if (plan->d_order) cudaFree(plan->d_order);
+                plan->d_order = nullptr;
+                plan->order_cap = 0;
+                KB_CUDA(cudaMalloc(&plan->d_order, sizeof(uint2) * n_tiles));
+                plan->order_cap = n_tiles;
+            }
+            KB_CUDA(cudaMemcpyAsync(plan->d_order, slow.data(), sizeof(uint2) * n_tiles, cudaMemcpyHostToDevice, st));
+            plan->v.tile_order = plan->d_order;
+            grid = dim3((unsigned)n_tiles, 1);
+        }
+    }
     switch (sv.nb) {
         case 4: launch_tiled_nb4(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
         case 2: launch_tiled_nb2(plan, sv, p, d_vx, d_vy, d_slots, grid, st); break;
@@ -522,7 +563,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
     if (!up || up->n_chunks <= 1) {
         if (up && up->n_chunks == 1) KB_CUDA(cudaStreamWaitEvent(st, up->ev[0], 0));
         plan->v.pixel_base = 0;
-        launch_tiled_any(plan, sv, p, d_vx, d_vy, d_slots, st);
+        launch_tiled_any(plan, sv, p, d_vx, d_vy, d_slots, st, !up);
         launches = 1;
     } else {
         // The stack is still arriving: search row bands as their rows land.  Band b ends where a tile's reach stays
@@ -544,7 +585,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
             KB_CUDA(cudaStreamWaitEvent(bs, up->ev[b], 0));
             const size_t row_off = (size_t)(ya - p.y_start_min) * sw;
             plan->v.pixel_base = (unsigned)row_off;
-            launch_tiled_any(plan, sv, pb, d_vx, d_vy, d_slots + row_off * p.results_per_pixel, bs);
+            launch_tiled_any(plan, sv, pb, d_vx, d_vy, d_slots + row_off * p.results_per_pixel, bs, false);
             used[k] = true;
             ++nb_launched;
             ++launches;

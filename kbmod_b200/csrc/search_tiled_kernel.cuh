@@ -89,6 +89,9 @@ struct PlanView {
     float *bar_out;
     // extent of the schedule's boxes relative to a tile's origin: [ext_x0, ext_x1) x [ext_y0, ext_y1) pixels
     int ext_x0, ext_x1, ext_y0, ext_y1;
+    // optional launch order of the tiles (1-D grid): tile_order[blockIdx.x] = {tile column, tile row}.  Tiles that
+    // count observations follow the longer single-image schedule and are started first.
+    const uint2 *tile_order;
 };
 
 struct TiledPlan {
@@ -97,6 +100,9 @@ struct TiledPlan {
     void *d_block = nullptr;  // one allocation holding all tables
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the gather kernel
     float ms_accum = 0.0f;    // gather-kernel time of the last search (summed over its chunks)
+    uint2 *d_order = nullptr; // tile launch order of the current launch (counting searches over run planes)
+    size_t order_cap = 0;
+    bool order_tiles = false; // the schedule has a longer single-image variant for the tiles that count
     size_t smem = 0;
     int reach_hi = 0;  // a tile at row y0 reads stack rows below y0 + reach_hi (largest box bottom, padded)
     int nb = 4, K = 8;
@@ -176,9 +182,11 @@ __device__ __forceinline__ void lh_bounds(float ps, float ph, float e_psi, float
     lb = (psi_lo >= 0.0f) ? psi_lo * rh * 0.999996f : psi_lo * rl * 1.000004f;
 }
 
-// The gather of one stage: for each of its nt images, the words of the lane's TPX pixels for the TG candidates.
+// The gather of one stage: for each of its nt records, the words of the lane's TPX pixels for the TG candidates.
 // DO_COUNT also counts the valid observations (word != 0: the quantiser never maps a valid pair to 0) with one compare
-// and one predicated add in place (the compiler's select form costs a move more).
+// and one predicated add in place (the compiler's select form costs a move more).  A run record counts as its m
+// images: it is only counted in stacks without invalid pixels, where a word is 0 exactly when the (common) pixel of
+// the run's images lies outside the image.
 template <int TG, bool DO_COUNT, int CT>
 __device__ __forceinline__ void gather_images(int nt, uint32_t rec, uint32_t lane_base, int warp, int (&P)[TPX][TG],
                                               int (&F)[TPX][TG], int (&cnt)[CT][CT == 1 ? 1 : TG]) {
@@ -202,10 +210,10 @@ __device__ __forceinline__ void gather_images(int nt, uint32_t rec, uint32_t lan
                 for (int h = 0; h < TPX; ++h) {
                     P[h][j] = __dp2a_lo((int)w[h], ir.z, P[h][j]);   // += m * low half  (psi, signed 16 bit)
                     F[h][j] = __dp2a_lo((int)w[h], ir.w, F[h][j]);   // += m * high half (phi)
-                    if (DO_COUNT) {
-                        asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}"
+                    if (DO_COUNT) {   // + the number of images the record stands for
+                        asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, %2;\n\t}"
                             : "+r"(cnt[h][j])
-                            : "r"(w[h]));
+                            : "r"(w[h]), "r"(ir.z));
                     }
                 }
             }
@@ -258,12 +266,14 @@ __global__ void __launch_bounds__(TNT, 1)
     __syncthreads();
 
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
-    const int tile_x0 = p.x_start_min + blockIdx.x * TBX, tile_y0 = p.y_start_min + blockIdx.y * TBY;
+    const uint2 tile = pv.tile_order ? pv.tile_order[blockIdx.x] : make_uint2(blockIdx.x, blockIdx.y);
+    const int tile_x0 = p.x_start_min + (int)tile.x * TBX, tile_y0 = p.y_start_min + (int)tile.y * TBY;
     constexpr int PB = kScreenPairBytes;
     constexpr int TG = group_size(SIGMAG);
     // Observations only have to be counted where some can be invalid: a stack with invalid pixels, or a tile from
-    // which some box of the schedule reaches over the image's edge (CTA-uniform).  Tiles that count follow the
-    // schedule of single images (a run's summed word cannot say how many of its images had data).
+    // which some box of the schedule reaches over the image's edge (CTA-uniform).  In a stack with invalid pixels the
+    // counting follows the schedule of single images (a run's summed word cannot say how many of its images had
+    // data there); the host only builds that second schedule for such stacks.
     const bool count_here = COUNT && !(sv.all_valid && tile_x0 + pv.ext_x0 >= 0 && tile_x0 + pv.ext_x1 <= sv.W &&
                                        tile_y0 + pv.ext_y0 >= 0 && tile_y0 + pv.ext_y1 <= sv.H);
     const StageRec *const stage_list = count_here ? pv.stages_plain : pv.stages;
