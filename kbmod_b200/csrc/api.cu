@@ -5,6 +5,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <omp.h>
+
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -217,14 +219,17 @@ struct PinnedRing {
 };
 static PinnedRing g_ring_up[64], g_ring_down[64];
 
-static void parallel_memcpy(void *dst, const void *src, size_t n) {
+// `share`: fraction of the host threads to use (the background fill of the host copy takes a quarter, so the
+// caller's own thread -- which is launching the first search meanwhile -- is not crowded out).
+static void parallel_memcpy(void *dst, const void *src, size_t n, int share_div = 1) {
     const size_t piece = 256u << 10;
     const long long np = (long long)((n + piece - 1) / piece);
     if (np <= 2) {
         memcpy(dst, src, n);
         return;
     }
-#pragma omp parallel for schedule(static)
+    const int nthreads = std::max(1, omp_get_max_threads() / std::max(share_div, 1));
+#pragma omp parallel for schedule(static) num_threads(nthreads)
     for (long long i = 0; i < np; ++i) {
         const size_t o = (size_t)i * piece;
         memcpy((char *)dst + o, (const char *)src + o, std::min(piece, n - o));
@@ -265,7 +270,7 @@ static void ring_d2h(int device, void *h_dst, const void *d_src, size_t bytes, c
     for (size_t c = 0; c < nchunks; ++c) {
         const int i = (int)(c % PinnedRing::kSlots);
         KB_CUDA(cudaEventSynchronize(r.ev[i]));
-        parallel_memcpy((char *)h_dst + c * S, r.slot[i], std::min(S, bytes - c * S));
+        parallel_memcpy((char *)h_dst + c * S, r.slot[i], std::min(S, bytes - c * S), 4);
         if (c + depth < nchunks) issue(c + depth);
     }
 }
@@ -281,7 +286,8 @@ static void alloc_host_array(kb_handle h, size_t bytes) {
     const bool band = h->row_lo != 0 || h->row_hi != h->H;
     if (!band) {
         const long long npages = (long long)((bytes + 4095) / 4096);
-#pragma omp parallel for schedule(static)
+        const int nthreads = std::max(1, omp_get_max_threads() / 4);   // runs beside the caller's first search
+#pragma omp parallel for schedule(static) num_threads(nthreads)
         for (long long i = 0; i < npages; ++i) c[(size_t)i * 4096] = 0;  // first touch
     } else {
         // band-limited handle: only its rows are ever written; the other pages stay untouched (and uncommitted)
