@@ -441,6 +441,8 @@ def run_ours(args, c, cfg_name):
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
     dist.set_device(local_rank)
+    # One process per GPU: keep this rank's host buffers (and the threads that fill them) on its GPU's own socket.
+    bound = dist.bind_to_device_cpus() if world > 1 and not os.environ.get("KB_NO_CPU_BINDING") else None
     comm = dist.Comm(rank, world) if world > 1 else None
 
     strong = args.scaling == "strong" and world > 1
@@ -543,6 +545,7 @@ def run_ours(args, c, cfg_name):
         h2d = tm["h2d_stack_bytes"]   # the rows this rank's band can reach (the whole stack for a full-frame search)
         res = s.get_results_array()
         d2h = res.nbytes
+    e2e_tm = tm
     ms_e2e_dev = s.timer_stop()
     wall_e2e = (time.perf_counter() - t0) * 1e3
     ms_e2e = max(ms_e2e_dev, wall_e2e) / e2e_steps  # results are read after the last kernel: use the wall clock
@@ -596,7 +599,8 @@ def run_ours(args, c, cfg_name):
             "e2e_first_search_ms": first_ms, "e2e_first_search": evals_job / (first_ms * 1e-3),
             "e2e_with_ctor_ms": with_ctor_ms, "e2e_with_ctor": evals_job / (with_ctor_ms * 1e-3),
             "ctor_seconds": ctor_s, "storage_dtype": {4: "f32", 2: "u16", 1: "u8"}[nbytes],
-            "first_search_device_ms": {k: first_tm[k] for k in ("ms_h2d", "ms_prepare", "ms_search", "ms_filter_sort", "ms_total")}}
+            "first_search_device_ms": {k: first_tm[k] for k in ("ms_h2d", "ms_prepare", "ms_search", "ms_filter_sort", "ms_total")},
+            "e2e_step_device_ms": {k: e2e_tm[k] for k in ("ms_h2d", "ms_prepare", "ms_search", "ms_filter_sort", "ms_total")}}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
@@ -620,6 +624,8 @@ def run_ours(args, c, cfg_name):
         # NCCL-merged list of all ranks against one GPU searching the whole frame alone (rank 0, outside the timing)
         merged = results_digest(s.get_results_array())
         line["ctor_seconds_max_over_ranks"] = comm.max_float(ctor_s)
+        line["host_cpus_rank0"] = (f"{len(bound)} CPUs local to the GPU (sysfs local_cpulist)" if bound
+                                   else "unbound (nothing narrower than the process mask reported)")
         if rank == 0:
             ymin, ymax = (0, c["H"]) if strong else (0, c["H"] * world)
             if c.get("band_div") and not strong:

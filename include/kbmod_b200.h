@@ -77,6 +77,10 @@ KB_EXPORT int kb_gpu_memory(size_t *free_bytes, size_t *total_bytes);
 /* Select the CUDA device for handles created afterwards by this thread (the reference always uses the current
  * device and never sets it: kernels/kernel_memory.cu; one process per GPU needs this). */
 KB_EXPORT int kb_set_device(int device);
+/* "domain:bus:device.function" of the current device (>= 16 bytes).  No reference counterpart: a multi-GPU host
+ * process uses it to find the CPUs of the GPU's own socket (/sys/bus/pci/devices/<id>/local_cpulist) so that the
+ * host copy of its stack and the pinned staging buffers are placed in that socket's memory. */
+KB_EXPORT int kb_device_pci_bus_id(char *buf, int len);
 
 /* ---- image operations (image_utils_cpp.cpp) ------------------------------------------------------ */
 /* convolve_image_gpu (:70-101) with the arithmetic of convolve_image_cpu (:20-68): mask-aware correlation,

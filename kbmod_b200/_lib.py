@@ -48,7 +48,7 @@ assert TRAJECTORY_DTYPE.itemsize == 28 and C.sizeof(KbTrajectory) == 28
 
 # Every symbol include/kbmod_b200.h declares (checked by tests/test_cabi_symbols.py against the header).
 SYMBOLS = [
-    "kb_last_error", "kb_version", "kb_device_count", "kb_gpu_memory", "kb_set_device", "kb_convolve", "kb_generate_psi_phi",
+    "kb_last_error", "kb_version", "kb_device_count", "kb_gpu_memory", "kb_set_device", "kb_device_pci_bus_id", "kb_convolve", "kb_generate_psi_phi",
     "kb_create_from_images", "kb_create_from_images_rows", "kb_create_from_psi_phi", "kb_destroy", "kb_get_meta", "kb_host_array",
     "kb_read_psi_phi", "kb_read_time", "kb_preload", "kb_unload", "kb_on_gpu", "kb_search", "kb_get_results",
     "kb_num_results", "kb_set_results", "kb_clear_results", "kb_get_timing", "kb_get_slots",

@@ -749,6 +749,15 @@ int kb_set_device(int device) {
     KB_API_END
 }
 
+int kb_device_pci_bus_id(char *buf, int len) {
+    KB_API_BEGIN
+    if (!buf || len < 16) throw Error("kb_device_pci_bus_id: need a buffer of at least 16 bytes");
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    KB_CUDA(cudaDeviceGetPCIBusId(buf, len, dev));
+    KB_API_END
+}
+
 static float host_sum(const float *k, int n) {
     float s = 0.0f;
     for (int i = 0; i < n; ++i) s += k[i];  // image_utils_cpp.cpp:30-35 row-major float adds

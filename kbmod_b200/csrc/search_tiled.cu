@@ -3,24 +3,32 @@
 // exactly only what the screening cannot rule out (see search_tiled_kernel.cuh).
 //
 // Decomposition (B200-first, not the reference's one-thread-per-pixel serial loop):
-//   * A CTA owns a tile of 32 x BY start pixels (one consumer warp per row, lanes along x) and visits the
-//     candidate list in *groups* of G candidates that are neighbours in velocity space.  Every consumer thread
-//     keeps the G running (psi_sum, phi_sum, count) triples in registers.
-//   * For a group g and an image t, all G trajectories of all tile pixels land inside one small box of the
-//     image: origin (tile + min offset), size (32 + spread_x) x (BY + spread_y).  A dedicated producer warp
-//     fetches those boxes with TMA (cp.async.bulk.tensor, 3-D map over [t][y][x-pairs]) into a ring of shared
-//     memory stages, several images per stage, signalling mbarriers.  Out-of-image parts of a box are filled by
-//     the TMA unit with NaN (float) / 0 (codes) -- exactly the reference's "outside the image = no data".
-//   * Consumers wait on the stage's mbarrier and gather from shared memory: lane l of row r reads the pair at
-//     (r + dy_j(t), l + dx_j(t)) -- x-adjacent lanes read adjacent pairs, so every 64-bit LDS is conflict-free.
-//     The per-(candidate, image) integer offsets dx, dy come from a table built on the host with the
-//     reference's fp64 arithmetic; the table arrives in the same stage by a 1-D bulk copy.
-//   * After the last image of a group the G sums are turned into likelihoods.  A cheap conservative test
-//     (MUFU.RSQ estimate against the current threshold) rejects almost everything; survivors take the exact
-//     IEEE path, the rare sigma-G candidates re-gather their observations (search_device.cuh), and winners
-//     enter the per-pixel top-K list held in registers (ordered by lh, then candidate index == the order the
-//     reference's in-order strict-'>' insertion produces).
-//   * Epilogue: the K winners per pixel are re-evaluated exactly to obtain flux and obs_count and written out.
+//   * A CTA owns a tile of 64 x 15 start pixels (one consumer warp per row, every lane two pixels: x and x + 32) and
+//     visits the candidate list in *groups* of G = 16 (sigma-G on) or 8 (off) candidates that are neighbours in
+//     velocity space.  Every consumer thread keeps the G running integer (psi, phi) sums of both its pixels in
+//     registers.
+//   * For a group and an image, all G trajectories of all tile pixels land inside one small box of the image:
+//     origin (tile + min offset), size (64 + spread_x) x (15 + spread_y).  A dedicated producer warp fetches those
+//     boxes of the SCREENING copy (one 32-bit word per pixel: two int16 in fixed point, 0 = no data) with TMA
+//     (cp.async.bulk.tensor, 3-D map over [plane][y][x]) into a ring of shared-memory stages, several images per
+//     stage, signalling mbarriers.  Out-of-image parts of a box are zero-filled by the TMA unit -- exactly the
+//     reference's "outside the image = no data".  The stage's schedule record arrives by a 1-D bulk copy.
+//   * Consumers wait on the stage's mbarrier and gather: lane l of row r reads the word at
+//     (r + dy_j(t), l + dx_j(t)) -- x-adjacent lanes read adjacent words, so every LDS.32 is conflict-free -- and adds
+//     its halves to the two sums with one IDP.2A each.  The per-(candidate, image) integer offsets dx, dy come from
+//     a table built on the host with the reference's fp64 arithmetic.
+//   * Run planes: exposures taken minutes apart (a run) mostly keep a candidate's pixel offset.  The screening copy
+//     carries one summed plane per run (and per half/quarter/pair of one); a group whose candidates all keep their
+//     offsets through a run gathers the run's plane once, with the run length as the IDP.2A multiplier.
+//   * After the last image of a group the integer sums give rigorous bounds of the exact float likelihood (see
+//     screen_bounds).  Sigma-G on: a pair whose upper bound cannot reach min_lh is dropped, the rest is queued for
+//     clip_kernel (warp-cooperative sigma-G with the reference's exact arithmetic).  Sigma-G off: the eight largest
+//     lower bounds per pixel are a rising bar; pairs whose upper bound reaches it are queued for exact_kernel.
+//     Survivors of either queue enter the per-pixel top-K lists (ordered by lh, then candidate index == the order
+//     the reference's in-order strict-'>' insertion produces) in surv_merge_kernel.  Only exactly evaluated values
+//     are ever written, so results are bit-identical to the reference's.
+//   * Observation counts (min_obs with sigma-G off) are only swept in tiles where an observation can be invalid (a
+//     stack with invalid pixels, or boxes that leave the image); elsewhere the count is T.
 //
 // Exactness of the offset table: the reference computes ix = floor((x + fl(vx*t)) + 0.5) in fp64 per pixel.
 // With |x|, |vx*t| < 2^22 the two roundings perturb the sum by < 2^-29, so ix = x + floor(fl(vx*t) + 0.5)

@@ -23,6 +23,42 @@ def set_device(local_rank):
     check(lib.kb_set_device(C.c_int(local_rank)))
 
 
+def parse_cpulist(text):
+    """The CPU numbers of a sysfs cpulist string ("0-31,64-95")."""
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_to_device_cpus():
+    """Restrict this process to the CPUs of its GPU's own socket (sysfs ``local_cpulist`` of the current device).
+
+    Call it after ``set_device`` and before the first stack is built: the threads the library starts later inherit
+    the mask, so the host copy of the stack (first touch) and the pinned staging buffers land in the memory the
+    GPU's PCIe root reads without crossing sockets.  With one process per GPU every socket then serves its own GPUs.
+    Returns the sorted CPU list it bound to, or None where the platform reports nothing narrower than the current
+    mask (virtual machines, single-socket hosts).  No reference counterpart (the reference is single-GPU).
+    """
+    buf = C.create_string_buffer(32)
+    check(lib.kb_device_pci_bus_id(buf, C.c_int(32)))
+    path = f"/sys/bus/pci/devices/{buf.value.decode().lower()}/local_cpulist"
+    try:
+        with open(path) as f:
+            local = parse_cpulist(f.read())
+        now = os.sched_getaffinity(0)
+        want = local & now
+        if not want or want == now:
+            return None
+        os.sched_setaffinity(0, want)
+        return sorted(want)
+    except (OSError, ValueError, AttributeError):
+        return None
+
+
 def row_bands(y_min, y_max, world):
     """Contiguous start-pixel row bands [y_k, y_{k+1}) covering [y_min, y_max), as even as possible."""
     n = y_max - y_min

@@ -65,6 +65,15 @@ def test_two_rank_shard_and_merge_equals_single_process(tmp_path):
         assert top.tobytes() == want[:50].tobytes()
 
 
+def test_parse_cpulist():
+    from kbmod_b200.dist import parse_cpulist
+    assert parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert parse_cpulist("5") == {5}
+    assert parse_cpulist("") == set()
+    with pytest.raises(ValueError):
+        parse_cpulist("a-b")
+
+
 def test_band_rows_cover_the_reach_of_a_band():
     from kbmod_b200.dist import band_rows
     vy = np.array([-3.5, 0.0, 2.0], dtype=np.float32)
