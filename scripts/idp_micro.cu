@@ -1,6 +1,6 @@
 // Pipe-rate probe for the integer screening loop: how many warp-instructions per clock per SM the device sustains for
 //   (0) dp2a (IDP.2A)   (1) 32-bit integer add (IADD3)   (2) FADD   (3) the loop shape LDS.32 + IADD + 2 x dp2a
-//   (4) the float loop shape LDS.64 + IADD + 2 x FADD
+//   (4) the float loop shape LDS.64 + IADD + 2 x FADD   (5, 6) LDS.32 + IADD + one IMAD / one add on a packed word
 // Build + run on the box:  nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o /tmp/idp scripts/idp_micro.cu && /tmp/idp
 #include <cstdio>
 #include <cstdint>
@@ -16,9 +16,15 @@ __global__ void __launch_bounds__(512, 1) probe(int iters, const int *offs_g, in
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sm) + (threadIdx.x & 31) * (MODE == 4 ? 8 : 4) + (threadIdx.x >> 5) * 1024;
     int a[16], b[16];
     float fa[16], fb[16];
+    const int mult = offs_g[64];
 #pragma unroll
     for (int j = 0; j < 16; ++j) { a[j] = j; b[j] = -j; fa[j] = j; fb[j] = -j; }
+    int offs_r[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) offs_r[j] = offs[j * 3];
+#pragma unroll 2
     for (int k = 0; k < iters; ++k) {
+        const uint32_t base_k = sbase + ((k & 15) << 7);   // the per-image part of the address, once per sweep
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             if (MODE == 0) {
@@ -32,13 +38,19 @@ __global__ void __launch_bounds__(512, 1) probe(int iters, const int *offs_g, in
                 fb[j] = fb[j] + 1.0f;
             } else if (MODE == 3) {
                 uint32_t w;
-                const uint32_t addr = sbase + offs[(j + k) & 63];
+                const uint32_t addr = base_k + offs_r[j];
                 asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
                 a[j] = __dp2a_lo((int)w, 0x0001, a[j]);
                 b[j] = __dp2a_lo((int)w, 0x0100, b[j]);
+            } else if (MODE == 5 || MODE == 6) {
+                uint32_t w;
+                const uint32_t addr = base_k + offs_r[j];
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
+                if (MODE == 5) a[j] = (int)w * mult + a[j];   // one IMAD: both packed sums at once, times the run length
+                else a[j] += (int)w;
             } else {
                 float x, y;
-                const uint32_t addr = sbase + offs[(j + k) & 63];
+                const uint32_t addr = base_k + offs_r[j];
                 asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(x), "=f"(y) : "r"(addr));
                 fa[j] += x;
                 fb[j] += y;
@@ -72,7 +84,7 @@ static void run(const char *name, int per_iter_instr, const int *d_offs, int *d_
 int main() {
     cudaDeviceProp prop; cudaGetDeviceProperties(&prop, 0);
     int clk_khz = 0; cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0);
-    int h_offs[64]; for (int i = 0; i < 64; ++i) h_offs[i] = ((i * 37) % 61) * 128 * 4 % 60000;
+    int h_offs[65]; h_offs[64] = 3; for (int i = 0; i < 64; ++i) h_offs[i] = ((i * 37) % 61) * 128 * 4 % 60000;
     for (int i = 0; i < 64; ++i) h_offs[i] &= ~7;
     int *d_offs, *d_out; cudaMalloc(&d_offs, sizeof(h_offs)); cudaMalloc(&d_out, 4);
     cudaMemcpy(d_offs, h_offs, sizeof(h_offs), cudaMemcpyHostToDevice);
@@ -82,5 +94,7 @@ int main() {
     run<2>("fadd x2", 2, d_offs, d_out, sms, hz);
     run<3>("lds32 + iadd + 2 dp2a", 4, d_offs, d_out, sms, hz);
     run<4>("lds64 + iadd + 2 fadd", 4, d_offs, d_out, sms, hz);
+    run<5>("lds32 + iadd + imad (packed sums)", 3, d_offs, d_out, sms, hz);
+    run<6>("lds32 + iadd + add (packed sums)", 3, d_offs, d_out, sms, hz);
     return 0;
 }
