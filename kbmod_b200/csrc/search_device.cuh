@@ -162,10 +162,10 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 // lh / flux (sums in time order; -1 when phi_sum <= 0) if there are too few observations or that lh is below min_lh
 // (kernels.cu:201-203: the clip is skipped), the clipped values otherwise.
 template <int NB, int E>
-__device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
-                                            float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float min_lh,
-                                            float &lh, float &flux, int &n_valid, bool &needs_serial,
-                                            float2 *ws = nullptr) {
+__device__ __forceinline__ void warp_sigmag_body(const StackView &sv, const double *times, int x, int y, float vx,
+                                                 float vy, float sgl_L, float sgl_H, float coeff, int min_obs,
+                                                 float min_lh, float &lh, float &flux, int &n_valid,
+                                                 bool &needs_serial, float2 *ws = nullptr) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     float a[E], b[E], lc[E];
@@ -355,6 +355,16 @@ __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *time
         }
     }
     finish_sums(ps, ph, lh, flux);
+}
+
+// Out of line for the search kernels (whose register budget belongs to the sweep); clip_kernel inlines the body.
+template <int NB, int E>
+__device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
+                                            float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float min_lh,
+                                            float &lh, float &flux, int &n_valid, bool &needs_serial,
+                                            float2 *ws = nullptr) {
+    warp_sigmag_body<NB, E>(sv, times, x, y, vx, vy, sgl_L, sgl_H, coeff, min_obs, min_lh, lh, flux, n_valid,
+                            needs_serial, ws);
 }
 
 template <int NB, bool SIGMAG, int MAXT>

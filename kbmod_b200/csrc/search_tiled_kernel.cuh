@@ -531,7 +531,18 @@ __global__ void __launch_bounds__(256)
         const int c = (int)it.y;
         float lh = -1.0f, flux = -1.0f;  // what the reference keeps when there is no valid observation at all
         int nv = 0;
-        sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, __ldg(cvx + c), __ldg(cvy + c), p, lh, flux, nv, ws);
+        const float vx = __ldg(cvx + c), vy = __ldg(cvy + c);
+        if constexpr (MAXT <= 256) {
+            // the request is warp-uniform: the cooperative routine in line, no hand-over between lanes
+            bool serial;
+            warp_sigmag_body<NB, (MAXT + 31) / 32>(sv, s_times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff,
+                                                   p.min_observations, p.min_lh, lh, flux, nv, serial, ws);
+            if (serial && lane == 0)   // tied lc values with different payloads: the reference's exchange-sort order
+                sigmag_recompute<NB, MAXT>(sv, s_times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
+                                           nullptr);
+        } else {
+            sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, vx, vy, p, lh, flux, nv, ws);
+        }
         if (lane == 0) {
             // Queued candidates only passed the screening bound.  sigmag_for_lanes returns what evaluateTrajectory
             // does (kernels.cu:154-242): the unclipped lh when it is below min_lh or there are too few
