@@ -145,8 +145,9 @@ KB_EXPORT int kb_get_slots(kb_handle h, kb_trajectory *out, uint64_t capacity, u
  * 3 = force the candidate-parallel kernel (small start windows with long per-pixel lists, as TrajectoryExplorer
  * drives StackSearch: trajectory_explorer.py:221-255). */
 KB_EXPORT int kb_set_kernel_mode(kb_handle h, int mode);
-/* Why the last kb_search on this handle did not run on the tiled kernel ("" when it did): borrowed string, valid
- * until the next search.  The Python layer logs it (the reference has one kernel and nothing to report). */
+/* Why the last kb_search on this handle did not run on the tiled kernel, or ran on it without its screening paying
+ * off (a sigma-G search that had to evaluate more than 5 % of its pairs exactly); "" otherwise.  Borrowed string,
+ * valid until the next search.  The Python layer logs it (the reference has one kernel and nothing to report). */
 KB_EXPORT int kb_search_note(kb_handle h, const char **note);
 
 /* StackSearch::evaluate_single_trajectory(trj, use_kernel=true) (stack_search.cpp:193-209 -> evaluateTrajectory

@@ -1212,6 +1212,19 @@ int kb_search(kb_handle h, const kb_params *params, const float *vx, const float
     uint64_t n_keep = 0;
     launches += filter_count(h->d_slots.p, n_slots, p.min_lh, p.min_observations, h->scratch, &n_keep, st);
     const float main_ms = plan ? tiled_plan_kernel_ms(plan) : -1.0f;   // the stream is idle (filter_count synchronised)
+    if (plan && p.do_sigmag_filter) {
+        // Screening that lets a large share of the pairs through has stopped paying: say so (results are unaffected).
+        const double pairs = (double)(p.x_start_max - p.x_start_min) * (double)(p.y_start_max - p.y_start_min) * (double)n_cand;
+        const double req = (double)tiled_plan_requests(plan);
+        if (pairs >= 1e8 && req > 0.05 * pairs) {
+            char buf[256];
+            snprintf(buf, sizeof(buf),
+                     "screening passed %.0f %% of the (start pixel, candidate) pairs on to exact evaluation: the stack's "
+                     "largest |psi| or phi is too far above its noise for the 16-bit screening copy (mask saturated "
+                     "pixels), or min_lh is low", 100.0 * req / pairs);
+            h->search_note = buf;
+        }
+    }
     h->d_results.ensure(std::max<uint64_t>(n_keep, 1));
     bool invalid = false;
     launches += filter_finish(h->d_slots.p, n_slots, n_keep, (int)p.results_per_pixel, (int)sw, p.x_start_min,

@@ -144,6 +144,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
                         const float *d_vy, Slot *d_slots, ClipScratch &clip, ResultScratch &scr, cudaStream_t st,
                         const UploadProgress *up = nullptr, bool *overflowed = nullptr, bool is_chunk = false);
 void tiled_plan_destroy(TiledPlan *plan);
+unsigned long long tiled_plan_requests(TiledPlan *plan);  // deferred exact evaluations queued by the last launch
 float tiled_plan_kernel_ms(TiledPlan *plan);  // duration of the gather kernel of the last launch (CUDA events)
 
 // psi_phi.cu

@@ -438,6 +438,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
 }
 
 float tiled_plan_kernel_ms(TiledPlan *plan) { return plan ? plan->ms_accum : 0.0f; }
+unsigned long long tiled_plan_requests(TiledPlan *plan) { return plan ? plan->requests_accum : 0ull; }
 
 void tiled_plan_destroy(TiledPlan *plan) {
     if (!plan) return;
@@ -497,6 +498,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
     const int sw = p.x_start_max - p.x_start_min, sh = p.y_start_max - p.y_start_min;
     if (!is_chunk) {
         plan->ms_accum = 0.0f;
+        plan->requests_accum = 0;
         if (overflowed) *overflowed = false;
     }
     if (!plan->sigmag && !up && !is_chunk) {
@@ -643,6 +645,7 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
         if (getenv("KB_DEBUG"))
             fprintf(stderr, "[kbmod_b200] deferred exact evaluations (%s): requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
                     plan->sigmag ? "sigma-G clips" : "bounds reached the bar", cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
+        if (cnt[0] <= clip.cap) plan->requests_accum += cnt[0];   // (an overflowed area is counted by its halves)
         if (cnt[0] > clip.cap) {
             // The queue was too small and requests were dropped.  Search the two halves of the area again, each with
             // the whole queue to itself (the slots are simply overwritten); a single row of tiles that still does not

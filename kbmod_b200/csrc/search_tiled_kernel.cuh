@@ -100,6 +100,7 @@ struct TiledPlan {
     void *d_block = nullptr;  // one allocation holding all tables
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // around the gather kernel
     float ms_accum = 0.0f;    // gather-kernel time of the last search (summed over its chunks)
+    unsigned long long requests_accum = 0;  // deferred exact evaluations the last search queued
     uint2 *d_order = nullptr; // tile launch order of the current launch (counting searches over run planes)
     size_t order_cap = 0;
     bool order_tiles = false; // the schedule has a longer single-image variant for the tiles that count

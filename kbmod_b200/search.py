@@ -555,6 +555,7 @@ class StackSearch:
         fill_psi_phi_array_from_image_arrays(self._ppa, num_bytes, sci, var, psfs, times, rows)
         self._preloaded = False
         self._result_cache = None
+        self.last_search_note = ""   # why the last search was slower than usual, if it was (kb_search_note)
         timer.stop()
 
     # -- getters ------------------------------------------------------------------------------------
@@ -680,8 +681,9 @@ class StackSearch:
         check(lib.kb_search(self._ppa._require(), C.byref(cp), ptr(vx), ptr(vy), C.c_uint64(vx.size), C.byref(n)))
         note = C.c_char_p()
         check(lib.kb_search_note(self._ppa._require(), C.byref(note)))
-        if note.value:   # the search ran, but not on the throughput kernel: say why
-            self._log.warning("kbmod_b200: " + note.value.decode("utf-8", "replace"))
+        self.last_search_note = note.value.decode("utf-8", "replace") if note.value else ""
+        if self.last_search_note:   # the search ran, but not at the throughput kernel's usual speed: say why
+            self._log.warning("kbmod_b200: " + self.last_search_note)
         self._log.debug(f"Core search returned {n.value} results after filtering by LH and min_obs.")
         timer.stop()
 
