@@ -23,6 +23,8 @@ roofline: the gather kernel against the shared-memory load peak, measured in thi
 parity / reference_gpu (N = 1): the unmodified reference's own CUDA search_all from oracle/_ref on the same GPU --
          result lists identical modulo exact lh ties, and its time.  merge_check (N > 1): the NCCL-merged list against
          one GPU searching the whole frame.  named_config (N > 1): BASELINE.json's C4, strong-scaled, ctor included.
+other_configs (N = 1, default run): C3 (uint16, uint8), C1, C4 and one band of C5, each constructed, searched once
+         and timed for a few resident steps; their headline numbers also as flat keys (c4_value, c5_band_ms_per_step ...).
 The stack (671 MB at N=1) is larger than the 126 MB L2, so no L2 flush is needed between iterations.
 Only the cpu_baseline, parity / reference_gpu legs and --impl reference touch oracle/ (the checker and the
 reference's own code), all outside the timed regions of our arm.
@@ -433,6 +435,58 @@ def named_config_leg(kb, dist, comm, rank, world, c, name):
     return rec
 
 
+def other_config_leg(kb, dist, name, shared=None):
+    """One more BASELINE.json config measured in the same single-GPU run (the driver runs only the default line):
+    construction from host images, one search + read-back, then a few timed resident steps.  C3 reuses C2's images
+    (they differ in the encoding only); C4 / C5 generate theirs block-seeded (make_band_inputs); C5, an 8-GPU config,
+    is measured as one of its 8 start-pixel row bands, with psi/phi built for the rows that band can reach."""
+    c = CONFIGS[name]
+    band = rows = None
+    if shared is not None:
+        stack, vx, vy = shared
+    elif "kbmodv1" in c:
+        stack, vx, vy = make_inputs(c, 1)
+    else:
+        import kbmod_b200.fake_data as fd
+        need = (0, c["H"])
+        if c.get("band_div"):
+            n = c["H"] // c["band_div"]
+            band = (c["H"] // 2 - n // 2, c["H"] // 2 - n // 2 + n)
+            times = np.asarray(fd.create_fake_times(c["T"], 57130.2, obs_per_day=c["obs_per_day"],
+                                                    intra_night_gap=c.get("intra", 0.01)), dtype=float)
+            gen = fd.VelocityGridSearch(*c["grid"]) if "grid" in c else fd.EclipticCenteredSearch(*c["ecliptic"])
+            rows = dist.band_rows(band, gen.to_arrays()[1], times - times[0], c["H"])
+            rad = fd.make_gaussian_kernel(c["psf"]).shape[0] // 2
+            need = (rows[0] - rad, rows[1] + rad)
+        stack, vx, vy = make_band_inputs(c, need)
+    t0 = time.perf_counter()
+    s = kb.StackSearch(stack.sci, stack.var, stack.psfs, stack.zeroed_times, c["nb"], rows=rows)
+    ctor_s = time.perf_counter() - t0
+    configure(s, c, band)
+    s.search_all((vx, vy), True)
+    n_res = len(s.get_results_array())
+    first_ms = 1e3 * (time.perf_counter() - t0)
+    heavy = c["T"] >= 100
+    steps = 2 if heavy else 5
+    for _ in range(1 if heavy else 3):
+        s.search_all((vx, vy), True)
+    s.timer_start()
+    k_ms = 0.0
+    for _ in range(steps):
+        s.search_all((vx, vy), True)
+        k_ms += s.last_timing()["ms_main_kernel"]
+    ms = s.timer_stop() / steps
+    tiled = s.last_timing()["used_tiled"]
+    start_rows = (band[1] - band[0]) if band else c["H"]
+    evals = c["W"] * start_rows * len(vx) * c["T"]
+    rec = {"workload": workload_name(name, c, 1), "steps": steps, "ms_per_step": ms, "value": evals / (ms * 1e-3),
+           "unit": UNIT, "gather_kernel_ms": k_ms / steps, "ctor_seconds": ctor_s,
+           "ctor_plus_first_search_ms": first_ms, "results": int(n_res),
+           "kernel": ("generic", "tiled", "candidate-parallel")[tiled]}
+    del s
+    return rec
+
+
 def run_ours(args, c, cfg_name):
     from kbmod_b200 import search as kb
     from kbmod_b200 import dist
@@ -664,6 +718,20 @@ def run_ours(args, c, cfg_name):
             line["vs_reference_gpu_e2e"] = e2e_value / line["reference_gpu"]["e2e_value"]
         except Exception as e:
             line["parity"] = {"vs": "reference_gpu", "unavailable": str(e)[:200]}
+    if world == 1 and cfg_name == "C2" and args.other_configs:
+        # BASELINE.json's other configs in the same driver-run line (flat copies of the headline numbers: a parser
+        # that drops nested objects still keeps them)
+        others = {}
+        for name in [n for n in args.other_configs.split(",") if n in CONFIGS and n != cfg_name]:
+            try:
+                rec = other_config_leg(kb, dist, name, shared=(stack, vx, vy) if name.startswith("C3") else None)
+                key = name.lower() + ("_band" if CONFIGS[name].get("band_div") else "")
+                for f in ("value", "ms_per_step", "gather_kernel_ms", "ctor_seconds"):
+                    line[f"{key}_{f}"] = rec[f]
+            except Exception as e:
+                rec = {"error": str(e)[:300]}
+            others[name] = rec
+        line["other_configs"] = others
     if comm is not None:
         comm.finalize()
     if rank == 0:
@@ -699,6 +767,9 @@ def main():
     ap.add_argument("--no-merge-check", action="store_true", help="N > 1: skip rank 0's whole-frame check of the merge")
     ap.add_argument("--named-config", default="C4", help="N > 1 (weak runs): also run this config strong-scaled, "
                     "construction included (BASELINE.json's multi-GPU workload); '' to skip")
+    ap.add_argument("--other-configs", default="C3u16,C3u8,C1,C4,C5",
+                    help="N = 1, config C2 (the default run): also measure these configs briefly and add them to the "
+                         "line; '' to skip")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = every GPU searches its own copy-sized band of an N-times taller frame (default, "
                          "the driver's scaling run); strong = the named frame, start-pixel rows split over the GPUs "
