@@ -161,16 +161,13 @@ __device__ __noinline__ void sigmag_recompute(const StackView &sv, const double 
 // What comes back is exactly what evaluateTrajectory leaves in the trajectory (kernels.cu:154-242): the unclipped
 // lh / flux (sums in time order; -1 when phi_sum <= 0) if there are too few observations or that lh is below min_lh
 // (kernels.cu:201-203: the clip is skipped), the clipped values otherwise.
+// The re-gather: lane l takes the observations t = l, l + 32, ...  Returns the number of valid ones.
 template <int NB, int E>
-__device__ __forceinline__ void warp_sigmag_body(const StackView &sv, const double *times, int x, int y, float vx,
-                                                 float vy, float sgl_L, float sgl_H, float coeff, int min_obs,
-                                                 float min_lh, float &lh, float &flux, int &n_valid,
-                                                 bool &needs_serial, float2 *ws = nullptr) {
+__device__ __forceinline__ int warp_sigmag_load(const StackView &sv, const double *times, int x, int y, float vx,
+                                                float vy, float (&a)[E], float (&b)[E], float (&lc)[E], bool (&ok)[E],
+                                                unsigned (&okm)[E]) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    float a[E], b[E], lc[E];
-    bool ok[E];
-    unsigned okm[E];
     int n = 0;
 #pragma unroll
     for (int e = 0; e < E; ++e) {
@@ -186,6 +183,18 @@ __device__ __forceinline__ void warp_sigmag_body(const StackView &sv, const doub
         okm[e] = __ballot_sync(FULL, ok[e]);
         n += __popc(okm[e]);
     }
+    return n;
+}
+
+// Everything after the re-gather (see above).
+template <int NB, int E>
+__device__ __forceinline__ void warp_sigmag_eval(const StackView &sv, const float (&a)[E], const float (&b)[E],
+                                                 const float (&lc)[E], const bool (&ok)[E], const unsigned (&okm)[E],
+                                                 int n, float sgl_L, float sgl_H, float coeff, int min_obs,
+                                                 float min_lh, float &lh, float &flux, int &n_valid,
+                                                 bool &needs_serial, float2 *ws = nullptr) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
     needs_serial = false;
     n_valid = n;
     {   // kernels.cu:175-197: the unclipped sums, valid observations in time order (every lane runs the same chain)
@@ -357,7 +366,145 @@ __device__ __forceinline__ void warp_sigmag_body(const StackView &sv, const doub
     finish_sums(ps, ph, lh, flux);
 }
 
-// Out of line for the search kernels (whose register budget belongs to the sweep); clip_kernel inlines the body.
+// ---- a cheap, certain "no" for the deferred clips -------------------------------------------------------------------
+// Of the (start pixel, candidate) pairs whose screening bound reaches min_lh only about one in a hundred survives the
+// clip (a trajectory that crosses one bright source has a high unclipped lh and a noise-level clipped one).  Whether
+// a pair is rejected does not need the reference's ordered float sums, only bounds of them:
+//   * the order statistics and the kept set are functions of the lc values alone (exact here);
+//   * two float sums of the same n numbers taken in different orders differ by at most 2 gamma_(n-1) sum|v_i|
+//     (gamma_k = k u / (1 - k u), u = 2^-24), so a sum taken by a warp reduction brackets the reference's.
+// warp_sigmag_rejects returns true only when the reference certainly rejects the pair (too few observations, or the
+// unclipped lh below min_lh, or the clipped lh below min_lh: kernels.cu:201-203,318-320); false means "evaluate".
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+// The largest of the lanes' values (finite floats, or "none" = -FLT_MAX..): one REDUX on order-preserving integers.
+__device__ __forceinline__ float warp_max_finite(float v, bool have) {
+    const unsigned bits = __float_as_uint(v);
+    const unsigned key = have ? (bits ^ ((bits >> 31) ? 0xffffffffu : 0x80000000u)) : 0u;
+    const unsigned m = __reduce_max_sync(0xffffffffu, key);
+    return __uint_as_float(m ^ ((m >> 31) ? 0x80000000u : 0xffffffffu));
+}
+// [lo, hi] certainly contains fl(psi_sum / fl(sqrt(phi_sum))) for the reference's sequential float sums of the same n
+// numbers that (sp, sf) are float sums of in some other order; sa = float sum of |psi_i|, all phi_i >= 0.
+// False: no statement (phi_sum may not be positive, overflow).
+__device__ __forceinline__ bool lh_interval(float sp, float sa, float sf, int n, float &lo, float &hi) {
+    const float g = __fmul_rn((float)n, 1.5e-7f);   // > 2 gamma_(n-1) (1 + gamma_n) = 1.2e-7 n for n <= 256
+    const float dp = __fmul_rn(g, sa) + 1e-30f, df = __fmul_rn(g, sf) + 1e-30f;
+    const float p_hi = sp + dp, p_lo = sp - dp, f_hi = sf + df, f_lo = sf - df;
+    if (!(f_lo > 0.0f) || !(f_hi < FLT_MAX) || !(fabsf(p_hi) < FLT_MAX) || !(fabsf(p_lo) < FLT_MAX)) return false;
+    const float s_lo = __fsqrt_rn(f_lo), s_hi = __fsqrt_rn(f_hi);
+    hi = p_hi >= 0.0f ? __fdiv_rn(p_hi, s_lo) : __fdiv_rn(p_hi, s_hi);
+    lo = p_lo >= 0.0f ? __fdiv_rn(p_lo, s_hi) : __fdiv_rn(p_lo, s_lo);
+    // the roundings of these few operations and of the reference's own square root and division: < 1e-6 relative
+    hi = hi + (fabsf(hi) * 4e-6f + 1e-30f);
+    lo = lo - (fabsf(lo) * 4e-6f + 1e-30f);
+    return true;
+}
+template <int E>
+__device__ __forceinline__ bool warp_sigmag_rejects(int T, const float (&a)[E], const float (&b)[E],
+                                                    const float (&lc)[E], const bool (&ok)[E], int n, float sgl_L,
+                                                    float sgl_H, float coeff, int min_obs, float min_lh) {
+    const unsigned FULL = 0xffffffffu;
+    if (n == 0) return false;        // lh = flux = -1 there: left to the exact routine
+    if (n < min_obs) return true;    // kernels.cu:318: obs_count < min_observations never enters the list
+    bool odd = false;                // a negative phi or a non-finite lc: no bounds
+    float sp = 0.0f, sa = 0.0f, sf = 0.0f;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        odd |= ok[e] && (b[e] < 0.0f || !(fabsf(lc[e]) < FLT_MAX));
+        if (ok[e]) {
+            sp = __fadd_rn(sp, a[e]);
+            sa = __fadd_rn(sa, fabsf(a[e]));
+            sf = __fadd_rn(sf, b[e]);
+        }
+    }
+    if (__any_sync(FULL, odd)) return false;
+    float lo, hi;
+    if (!lh_interval(warp_sum(sp), warp_sum(sa), warp_sum(sf), n, lo, hi)) return false;
+    if (hi < min_lh) return true;    // kernels.cu:201-203: the clip is skipped, and :318-320 drops lh < min_lh
+    if (!(lo >= min_lh)) return false;
+    // The clip happens.  cnt[e] = number of strictly smaller values; the value at sorted position p is the largest
+    // one with cnt <= p (equal values included, whatever their order).
+    float lcs[E];
+    int cnt[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        lcs[e] = ok[e] ? lc[e] : KB_NAN_F;
+        cnt[e] = 0;
+    }
+#pragma unroll
+    for (int es = 0; es < E; ++es) {
+        const int nsrc = min(32, T - es * 32);  // warp-uniform
+#pragma unroll 4
+        for (int ls = 0; ls < nsrc; ++ls) {
+            const float v = __shfl_sync(FULL, lcs[es], ls);
+#pragma unroll
+            for (int e = 0; e < E; ++e) cnt[e] += (v < lcs[e]) ? 1 : 0;
+        }
+    }
+    // kernels.cu:94-127 percentile positions
+    if ((double)sgl_L < 0.0001) sgl_L = (float)0.0001;
+    if ((double)sgl_H > 0.9999) sgl_H = (float)0.9999;
+    int pL = (int)((double)ceilf(__fmul_rn((float)n, sgl_L)) + 0.001) - 1;
+    pL = pL < 0 ? 0 : pL;
+    pL = pL >= n ? n - 1 : pL;
+    int pH = (int)((double)ceilf(__fmul_rn((float)n, sgl_H)) + 0.001) - 1;
+    pH = pH < 0 ? 0 : pH;
+    pH = pH >= n ? n - 1 : pH;
+    int med = (int)(ceil((double)n * 0.5) + 0.001) - 1;
+    med = med < 0 ? 0 : med;
+    med = med >= n ? n - 1 : med;
+    float vL = -FLT_MAX, vH = -FLT_MAX, vM = -FLT_MAX;
+    bool hL = false, hH = false, hM = false;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        if (ok[e] && cnt[e] <= pL) { vL = hL ? fmaxf(vL, lc[e]) : lc[e]; hL = true; }
+        if (ok[e] && cnt[e] <= pH) { vH = hH ? fmaxf(vH, lc[e]) : lc[e]; hH = true; }
+        if (ok[e] && cnt[e] <= med) { vM = hM ? fmaxf(vM, lc[e]) : lc[e]; hM = true; }
+    }
+    vL = warp_max_finite(vL, hL);
+    vH = warp_max_finite(vH, hH);
+    vM = warp_max_finite(vM, hM);
+    // kernels.cu:130-146: the kept range of sorted positions == the values inside [lo_c, hi_c] (sorted, sigma_g >= 0)
+    const float sigma_g = __fmul_rn(coeff, __fsub_rn(vH, vL));
+    const float w = __fmul_rn(2.0f, sigma_g);
+    const float lo_c = __fsub_rn(vM, w), hi_c = __fadd_rn(vM, w);
+    if (!(fabsf(lo_c) < FLT_MAX) || !(fabsf(hi_c) < FLT_MAX) || !(lo_c <= vM) || !(vM <= hi_c)) return false;
+    sp = 0.0f;
+    sa = 0.0f;
+    sf = 0.0f;
+    int nk = 0;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        const bool keep = ok[e] && lc[e] >= lo_c && lc[e] <= hi_c;
+        nk += __popc(__ballot_sync(FULL, keep));
+        if (keep) {
+            sp = __fadd_rn(sp, a[e]);
+            sa = __fadd_rn(sa, fabsf(a[e]));
+            sf = __fadd_rn(sf, b[e]);
+        }
+    }
+    if (!lh_interval(warp_sum(sp), warp_sum(sa), warp_sum(sf), nk, lo, hi)) return false;
+    return hi < min_lh;              // kernels.cu:318-320: the clipped lh is below min_lh
+}
+
+template <int NB, int E>
+__device__ __forceinline__ void warp_sigmag_body(const StackView &sv, const double *times, int x, int y, float vx,
+                                                 float vy, float sgl_L, float sgl_H, float coeff, int min_obs,
+                                                 float min_lh, float &lh, float &flux, int &n_valid,
+                                                 bool &needs_serial, float2 *ws = nullptr) {
+    float a[E], b[E], lc[E];
+    bool ok[E];
+    unsigned okm[E];
+    const int n = warp_sigmag_load<NB, E>(sv, times, x, y, vx, vy, a, b, lc, ok, okm);
+    warp_sigmag_eval<NB, E>(sv, a, b, lc, ok, okm, n, sgl_L, sgl_H, coeff, min_obs, min_lh, lh, flux, n_valid,
+                            needs_serial, ws);
+}
+
+// Out of line for the search kernels (whose register budget belongs to the sweep); clip_kernel inlines the parts.
 template <int NB, int E>
 __device__ __noinline__ void warp_sigmag(const StackView &sv, const double *times, int x, int y, float vx,
                                             float vy, float sgl_L, float sgl_H, float coeff, int min_obs, float min_lh,

@@ -643,8 +643,9 @@ int launch_search_tiled(TiledPlan *plan, const StackView &sv, const kb_params &p
             KB_CUDA(cudaMemsetAsync(clip.counters + 1, 0, sizeof(unsigned long long), st));
         }
         if (getenv("KB_DEBUG"))
-            fprintf(stderr, "[kbmod_b200] deferred exact evaluations (%s): requests=%llu (queue cap %llu) survivors=%llu in-line=%llu\n",
-                    plan->sigmag ? "sigma-G clips" : "bounds reached the bar", cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2]);
+            fprintf(stderr, "[kbmod_b200] deferred exact evaluations (%s): requests=%llu (queue cap %llu) survivors=%llu in-line=%llu"
+                            " certain rejections (counted by a KB_CLIP_VERIFY build only)=%llu\n",
+                    plan->sigmag ? "sigma-G clips" : "bounds reached the bar", cnt[0], (unsigned long long)clip.cap, cnt[1], cnt[2], cnt[3]);
         if (cnt[0] <= clip.cap) plan->requests_accum += cnt[0];   // (an overflowed area is counted by its halves)
         if (cnt[0] > clip.cap) {
             // The queue was too small and requests were dropped.  Search the two halves of the area again, each with

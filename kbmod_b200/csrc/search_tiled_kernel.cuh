@@ -533,17 +533,38 @@ __global__ void __launch_bounds__(256)
         float lh = -1.0f, flux = -1.0f;  // what the reference keeps when there is no valid observation at all
         int nv = 0;
         const float vx = __ldg(cvx + c), vy = __ldg(cvy + c);
+        bool rejected = false;
         if constexpr (MAXT <= 256) {
             // the request is warp-uniform: the cooperative routine in line, no hand-over between lanes
+            constexpr int E = (MAXT + 31) / 32;
+            float oa[E], ob[E], olc[E];
+            bool ook[E];
+            unsigned ookm[E];
+            const int n_obs = warp_sigmag_load<NB, E>(sv, s_times, x, y, vx, vy, oa, ob, olc, ook, ookm);
+            // most requests are certainly rejected (bounds of the float sums): no ordered sums for those
+            rejected = warp_sigmag_rejects<E>(sv.T, oa, ob, olc, ook, n_obs, p.sgl_L, p.sgl_H, p.sigmag_coeff,
+                                              p.min_observations, p.min_lh);
+#ifndef KB_CLIP_VERIFY
+            if (rejected) continue;
+#endif
             bool serial;
-            warp_sigmag_body<NB, (MAXT + 31) / 32>(sv, s_times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff,
-                                                   p.min_observations, p.min_lh, lh, flux, nv, serial, ws);
+            warp_sigmag_eval<NB, E>(sv, oa, ob, olc, ook, ookm, n_obs, p.sgl_L, p.sgl_H, p.sigmag_coeff,
+                                    p.min_observations, p.min_lh, lh, flux, nv, serial, ws);
             if (serial && lane == 0)   // tied lc values with different payloads: the reference's exchange-sort order
                 sigmag_recompute<NB, MAXT>(sv, s_times, x, y, vx, vy, p.sgl_L, p.sgl_H, p.sigmag_coeff, lh, flux,
                                            nullptr);
         } else {
             sigmag_for_lanes<NB, MAXT>(lane == 0, sv, s_times, x, y, vx, vy, p, lh, flux, nv, ws);
         }
+#ifdef KB_CLIP_VERIFY
+        if constexpr (MAXT <= 256) {   // test build: every "certain" rejection against the exact routine
+            if (lane == 0 && rejected) atomicAdd(cnt + 3, 1ull);
+            if (lane == 0 && rejected && !(nv < p.min_observations) && !(lh < p.min_lh)) {
+                printf("kbmod_b200: warp_sigmag_rejects dropped pixel %u cand %d with lh %.9g nv %d\n", it.x, c, lh, nv);
+                __trap();
+            }
+        }
+#endif
         if (lane == 0) {
             // Queued candidates only passed the screening bound.  sigmag_for_lanes returns what evaluateTrajectory
             // does (kernels.cu:154-242): the unclipped lh when it is below min_lh or there are too few
