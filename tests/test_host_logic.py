@@ -110,3 +110,66 @@ def test_post_search_mirrors_validate_before_touching_the_gpu():
     with pytest.raises(ValueError):
         coadd_stamps(img, img, [0.0, 1.0, 2.0], [1, 2], [1], [0.0], [0.0], 2)   # ragged trajectory columns
     assert mjd_to_day(60000) == "2023-02-25" and mjd_to_day(60000.99) == "2023-02-25"
+
+
+# ---- the bound behind clip_kernel's certain rejections (search_device.cuh: warp_sum, lh_interval) ------------------
+def _warp_tree_sum(v):
+    """float32 sum of v the way the kernel takes it: lane l adds elements l, l + 32, ... in order, then a butterfly."""
+    f = np.float32
+    lanes = np.zeros(32, dtype=f)
+    for i, x in enumerate(v):
+        lanes[i % 32] = f(lanes[i % 32] + f(x))
+    d = 16
+    while d:
+        lanes = (lanes + lanes[np.arange(32) ^ d]).astype(f)
+        d >>= 1
+    return lanes[0]
+
+
+def _lh_interval(sp, sa, sf, n):
+    f = np.float32
+    g = f(f(n) * f(1.5e-7))
+    dp, df = f(f(g * sa) + f(1e-30)), f(f(g * sf) + f(1e-30))
+    p_hi, p_lo, f_hi, f_lo = f(sp + dp), f(sp - dp), f(sf + df), f(sf - df)
+    if not (f_lo > 0):
+        return None
+    s_lo, s_hi = np.sqrt(f_lo, dtype=f), np.sqrt(f_hi, dtype=f)
+    hi = f(p_hi / s_lo) if p_hi >= 0 else f(p_hi / s_hi)
+    lo = f(p_lo / s_hi) if p_lo >= 0 else f(p_lo / s_lo)
+    hi = f(hi + f(f(abs(hi)) * f(4e-6) + f(1e-30)))
+    lo = f(lo - f(f(abs(lo)) * f(4e-6) + f(1e-30)))
+    return lo, hi
+
+
+def test_bracketed_sums_contain_the_sequential_sum():
+    """A float sum taken by warp reduction, widened by 1.5e-7 n sum|v|, brackets the reference's sequential float sum
+    of the same numbers, and the lh interval built from two such sums contains the reference's lh -- for sums with
+    heavy cancellation, outliers and every n up to 256."""
+    rng = np.random.default_rng(5)
+    f = np.float32
+    for trial in range(400):
+        n = int(rng.integers(1, 257))
+        psi = rng.normal(0, 1, n).astype(f) * f(10.0 ** rng.uniform(-3, 3))
+        if trial % 3 == 0:
+            psi[rng.integers(0, n)] += f(10.0 ** rng.uniform(0, 6))       # one bright source on the trajectory
+        if trial % 5 == 0:
+            psi = np.concatenate([psi, -psi])[:n]                         # near-total cancellation
+        phi = (rng.random(n).astype(f) + f(0.01)) * f(10.0 ** rng.uniform(-4, 4))
+        seq_p = seq_f = f(0)
+        for a, b in zip(psi, phi):                                        # kernels.cu:175-197, time order
+            seq_p, seq_f = f(seq_p + a), f(seq_f + b)
+        sp, sa, sf = _warp_tree_sum(psi), _warp_tree_sum(np.abs(psi)), _warp_tree_sum(phi)
+        g = f(f(n) * f(1.5e-7))
+        assert abs(float(sp) - float(seq_p)) <= float(g) * float(sa) + 1e-30
+        assert abs(float(sf) - float(seq_f)) <= float(g) * float(sf) + 1e-30
+        iv = _lh_interval(sp, sa, sf, n)
+        assert iv is not None
+        ref_lh = f(seq_p / np.sqrt(seq_f, dtype=f))                      # kernels.cu:195-197
+        assert iv[0] <= ref_lh <= iv[1], (n, iv, ref_lh)
+        # and in a sorted (ascending psi/phi) order, the order of the clipped re-sum (kernels.cu:233-237)
+        order = np.argsort(psi / phi, kind="stable")
+        seq_p = seq_f = f(0)
+        for a, b in zip(psi[order], phi[order]):
+            seq_p, seq_f = f(seq_p + a), f(seq_f + b)
+        ref_lh = f(seq_p / np.sqrt(seq_f, dtype=f))
+        assert iv[0] <= ref_lh <= iv[1], (n, iv, ref_lh)
