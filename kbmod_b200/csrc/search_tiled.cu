@@ -35,6 +35,7 @@
 // unless fl(vx*t)+0.5 lies within 2^-27 of an integer without being exactly one.  Candidates with such an
 // image are not tabulated; every thread evaluates them with the exact per-pixel routine instead.
 #include <cuda.h>
+#include <chrono>
 #include <float.h>
 #include <math.h>
 #include <stdio.h>
@@ -77,7 +78,8 @@ static inline bool tab_offset(float v, double t, int &off) {
         return false;
     }
     const double q = prod + 0.5;
-    const double fl = floor(q);
+    double fl = (double)(long long)q;    // floor without the libm call: |q| < 2^22 + 1, truncate then step down
+    if (fl > q) fl -= 1.0;
     off = (int)fl;
     const double r = q - fl;
     const double dist = (r < 0.5) ? r : 1.0 - r;
@@ -104,6 +106,14 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     };
     const int T = sv.T, K = (int)p.results_per_pixel;
     const int TG = group_size(p.do_sigmag_filter != 0);   // candidates per group of this schedule
+    const bool dbg = getenv("KB_DEBUG") != nullptr;
+    auto t_phase = std::chrono::steady_clock::now();
+    auto phase = [&](const char *what) {
+        if (!dbg) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[kbmod_b200] tiled plan: %-28s %.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_phase).count());
+        t_phase = now;
+    };
     if (K > kMaxRegK) return no("results_per_pixel > 8");
     if (n_cand == 0) return no("no candidates");
     if (p.do_sigmag_filter && T > kMaxTSigma) return no("too many images for sigma-G");
@@ -129,15 +139,21 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     const int N = (int)n_cand;
     std::vector<int> exact, tabulated;
     tabulated.reserve(N);
-    for (int c = 0; c < N; ++c) {
-        bool ok = true;
-        for (int t = 0; t < T && ok; ++t) {
-            int o;
-            ok = tab_offset(h_vx[c], times[t], o) && tab_offset(h_vy[c], times[t], o);
+    {
+        std::vector<uint8_t> tab_ok((size_t)N);
+#pragma omp parallel for schedule(static)
+        for (int c = 0; c < N; ++c) {
+            bool ok = true;
+            for (int t = 0; t < T && ok; ++t) {
+                int o;
+                ok = tab_offset(h_vx[c], times[t], o) && tab_offset(h_vy[c], times[t], o);
+            }
+            tab_ok[c] = ok ? 1 : 0;
         }
-        (ok ? tabulated : exact).push_back(c);
+        for (int c = 0; c < N; ++c) (tab_ok[c] ? tabulated : exact).push_back(c);
     }
     const int NTab = (int)tabulated.size();
+    phase("tabulation test");
 
     // ---- group the rest: k-d style recursive bisection of velocity space into leaves of <= TG candidates ---------
     // A group's box is (TBX + sx) x (TBY + sy) pixels with sx, sy ~ velocity extent * max|t|; each cut goes
@@ -219,6 +235,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     }
     const int n_groups = (int)group_start.size() - 1;
     if (n_groups == 0 && exact.empty()) return no("no candidates");
+    phase("grouping");
     // Box widths come in steps (one tensor map each); a box is as wide as its own (group, image) needs.
     const int w_step = bw_round, w_base = TBX + w_step;
     const int w_max = std::min(w_base + (NMAPS - 1) * w_step, bw_limit);
@@ -239,99 +256,123 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     for (auto &v : run_at)
         std::stable_sort(v.begin(), v.end(), [&](int a, int b2) { return h_runs[a].y > h_runs[b2].y; });
     long long n_records[2] = {0, 0};
-    auto build = [&](bool use_runs, std::vector<StageRec> &stages) -> const char * {
+    // Stage records of a schedule in one plain buffer (no value-initialisation of 100+ MB).
+    struct StageBuf {
+        StageRec *p = nullptr;
+        size_t n = 0;
+        StageBuf() = default;
+        StageBuf(const StageBuf &) = delete;
+        StageBuf &operator=(const StageBuf &) = delete;
+        ~StageBuf() { free(p); }
+        bool empty() const { return n == 0; }
+        size_t size() const { return n; }
+        const StageRec *data() const { return p; }
+    };
+    // The records of group g, packed greedily into stages of <= STAGE_BYTES.
+    auto pack_group = [&](int g, bool use_runs, std::vector<StageRec> &out, long long &records, bool &overflow) {
+        const int b = group_start[g], n = group_start[g + 1] - b;
+        for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
+        // pixel offsets of the group's candidates at every image, once
+        std::vector<int> off_x((size_t)T * TGMAX), off_y((size_t)T * TGMAX);
+        for (int j = 0; j < n; ++j) {
+            const int c = tabulated[b + j];
+            for (int t = 0; t < T; ++t) {
+                tab_offset(h_vx[c], times[t], off_x[(size_t)t * TGMAX + j]);
+                tab_offset(h_vy[c], times[t], off_y[(size_t)t * TGMAX + j]);
+            }
+        }
+        out.reserve((size_t)T / 6 + 2);
+        StageRec cur;
+        memset(&cur, 0, sizeof(cur));
+        int nt = 0, used = 0, tx = 0, t0 = 0;
+        auto flush = [&](bool last) {
+            cur.meta = make_int4(nt | ((last ? 1 : 0) << 8), g, t0, tx + (int)sizeof(StageRec));
+            out.push_back(cur);
+            memset(&cur, 0, sizeof(cur));
+            nt = used = tx = 0;
+        };
+        for (int t = 0; t < T;) {
+            int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+            const int *dx = &off_x[(size_t)t * TGMAX], *dy = &off_y[(size_t)t * TGMAX];
+            for (int j = 0; j < n; ++j) {
+                mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
+                mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
+            }
+            int plane = t, mult = 1;
+            if (use_runs && !run_at[t].empty()) {
+                // how many images from t on do all candidates stay on their pixels?  the longest run that
+                // starts here and fits is read as one record
+                const int longest = h_runs[run_at[t][0]].y;
+                int hold = 1;
+                for (; hold < longest; ++hold) {
+                    const int *hx = &off_x[(size_t)(t + hold) * TGMAX], *hy = &off_y[(size_t)(t + hold) * TGMAX];
+                    bool same = true;
+                    for (int j = 0; j < n && same; ++j) same = hx[j] == dx[j] && hy[j] == dy[j];
+                    if (!same) break;
+                }
+                for (int r : run_at[t])
+                    if (h_runs[r].y <= hold) {
+                        plane = T + r;
+                        mult = h_runs[r].y;
+                        break;
+                    }
+            }
+            mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
+            const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
+            const int widx = std::max(0, (need_w - w_base + w_step - 1) / w_step);
+            const int pitch = w_base + w_step * widx;
+            const int rows_pad = (nrows + TCH - 1) / TCH * TCH;
+            const int bytes = rows_pad * pitch * PB;
+            if (pitch > w_max || widx >= NMAPS || nrows > rmax || nrows > 255 || bytes > STAGE_BYTES) {
+                overflow = true;
+                break;
+            }
+            if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
+            if (nt == 0) t0 = t;
+            cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 8) | (plane << 12), used);
+            group_reach[g] = std::max(group_reach[g], mny + rows_pad);
+            group_ext[g].x = std::min(group_ext[g].x, mnx);
+            group_ext[g].y = std::max(group_ext[g].y, mnx + pitch);
+            group_ext[g].z = std::min(group_ext[g].z, mny);
+            group_ext[g].w = std::max(group_ext[g].w, mny + rows_pad);
+            cur.img[nt].slot_off = used;
+            cur.img[nt].pitch_bytes = pitch * PB;
+            cur.img[nt].mult_lo = mult;         // byte 0: multiplies the low half of the word (psi)
+            cur.img[nt].mult_hi = mult << 8;    // byte 1: multiplies the high half (phi)
+            for (int j = 0; j < TGMAX; ++j)
+                cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
+            used += bytes;
+            tx += bytes;
+            ++nt;
+            ++records;
+            t += mult;
+        }
+        if (nt > 0) flush(true);
+    };
+    auto build = [&](bool use_runs, StageBuf &stages) -> const char * {
         std::vector<std::vector<StageRec>> per_group(std::max(n_groups, 1));
         bool overflow = false;
         long long records = 0;
-#pragma omp parallel for schedule(dynamic, 8) reduction(+ : records)
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : records) reduction(|| : overflow)
         for (int g = 0; g < n_groups; ++g) {
-            const int b = group_start[g], n = group_start[g + 1] - b;
-            int dx[TGMAX], dy[TGMAX];
-            for (int j = 0; j < n; ++j) cand[(size_t)g * TG + j] = tabulated[b + j];
-            std::vector<StageRec> &out = per_group[g];
-            StageRec cur;
-            memset(&cur, 0, sizeof(cur));
-            int nt = 0, used = 0, tx = 0, t0 = 0;
-            auto flush = [&](bool last) {
-                cur.meta = make_int4(nt | ((last ? 1 : 0) << 8), g, t0, tx + (int)sizeof(StageRec));
-                out.push_back(cur);
-                memset(&cur, 0, sizeof(cur));
-                nt = used = tx = 0;
-            };
-            for (int t = 0; t < T;) {
-                int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
-                for (int j = 0; j < n; ++j) {
-                    const int c = tabulated[b + j];
-                    tab_offset(h_vx[c], times[t], dx[j]);
-                    tab_offset(h_vy[c], times[t], dy[j]);
-                    mnx = std::min(mnx, dx[j]); mxx = std::max(mxx, dx[j]);
-                    mny = std::min(mny, dy[j]); mxy = std::max(mxy, dy[j]);
-                }
-                int plane = t, mult = 1;
-                if (use_runs && !run_at[t].empty()) {
-                    // how many images from t on do all candidates stay on their pixels?  the longest run that
-                    // starts here and fits is read as one record
-                    const int longest = h_runs[run_at[t][0]].y;
-                    int hold = 1;
-                    for (; hold < longest; ++hold) {
-                        bool same = true;
-                        for (int j = 0; j < n && same; ++j) {
-                            const int c = tabulated[b + j];
-                            int ox, oy;
-                            tab_offset(h_vx[c], times[t + hold], ox);
-                            tab_offset(h_vy[c], times[t + hold], oy);
-                            same = ox == dx[j] && oy == dy[j];
-                        }
-                        if (!same) break;
-                    }
-                    for (int r : run_at[t])
-                        if (h_runs[r].y <= hold) {
-                            plane = T + r;
-                            mult = h_runs[r].y;
-                            break;
-                        }
-                }
-                mnx -= ((p.x_start_min + mnx) % XA + XA) % XA;  // tile origins are multiples of 32 past x_start_min
-                const int need_w = TBX + (mxx - mnx), nrows = TBY + (mxy - mny);
-                const int widx = std::max(0, (need_w - w_base + w_step - 1) / w_step);
-                const int pitch = w_base + w_step * widx;
-                const int rows_pad = (nrows + TCH - 1) / TCH * TCH;
-                const int bytes = rows_pad * pitch * PB;
-                if (pitch > w_max || widx >= NMAPS || nrows > rmax || nrows > 255 || bytes > STAGE_BYTES) {
-                    overflow = true;
-                    break;
-                }
-                if (nt == TMAXTC || used + bytes > STAGE_BYTES) flush(false);
-                if (nt == 0) t0 = t;
-                cur.box[nt] = make_int4(mnx, mny, nrows | (widx << 8) | (plane << 12), used);
-                group_reach[g] = std::max(group_reach[g], mny + rows_pad);
-                group_ext[g].x = std::min(group_ext[g].x, mnx);
-                group_ext[g].y = std::max(group_ext[g].y, mnx + pitch);
-                group_ext[g].z = std::min(group_ext[g].z, mny);
-                group_ext[g].w = std::max(group_ext[g].w, mny + rows_pad);
-                cur.img[nt].slot_off = used;
-                cur.img[nt].pitch_bytes = pitch * PB;
-                cur.img[nt].mult_lo = mult;         // byte 0: multiplies the low half of the word (psi)
-                cur.img[nt].mult_hi = mult << 8;    // byte 1: multiplies the high half (phi)
-                for (int j = 0; j < TGMAX; ++j)
-                    cur.img[nt].offs[j] = (j < n) ? ((dy[j] - mny) * pitch + (dx[j] - mnx)) * PB : 0;
-                used += bytes;
-                tx += bytes;
-                ++nt;
-                ++records;
-                t += mult;
-            }
-            if (nt > 0) flush(true);
+            bool ov = false;
+            pack_group(g, use_runs, per_group[g], records, ov);
+            overflow = overflow || ov;
         }
         n_records[use_runs ? 1 : 0] = records;
         if (overflow) return "velocity spread too large for a shared-memory stage";
-        size_t total = 0;
-        for (auto &v : per_group) total += v.size();
+        std::vector<size_t> first((size_t)n_groups + 1, 0);
+        for (int g = 0; g < n_groups; ++g) first[(size_t)g + 1] = first[g] + per_group[g].size();
+        const size_t total = first[n_groups];
         if (total >= (1ull << 31)) return "too many stages";
-        stages.reserve(std::max<size_t>(total, 1));
-        for (auto &v : per_group) {
-            stages.insert(stages.end(), v.begin(), v.end());
-            std::vector<StageRec>().swap(v);
+        stages.p = static_cast<StageRec *>(malloc(std::max<size_t>(total, 1) * sizeof(StageRec)));
+        if (!stages.p) return "out of host memory for the schedule";
+        stages.n = total;
+#pragma omp parallel for schedule(dynamic, 64)
+        for (int g = 0; g < n_groups; ++g) {
+            if (!per_group[g].empty())
+                memcpy(stages.p + first[g], per_group[g].data(), per_group[g].size() * sizeof(StageRec));
+            std::vector<StageRec>().swap(per_group[g]);
         }
         return nullptr;
     };
@@ -340,12 +381,20 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     // summed word cannot say how many of its images had data; without invalid pixels it is all or none of them).
     const bool have_runs = sv.n_runs > 0 && h_runs != nullptr;
     const bool counting = !p.do_sigmag_filter && p.min_observations > 0;
-    std::vector<StageRec> stages, stages_plain;
+    StageBuf stages, stages_plain;
     if (const char *err = build(have_runs, stages)) return no(err);
     if (have_runs && counting && !sv.all_valid)
         if (const char *err = build(false, stages_plain)) return no(err);
     const int n_stages = (int)stages.size();
-    if (getenv("KB_DEBUG"))
+    phase("stage records");
+    if (dbg && getenv("KB_DEBUG_PLAN_HASH")) {
+        unsigned long long hsh = 1469598103934665603ull;
+        const unsigned char *q = reinterpret_cast<const unsigned char *>(stages.data());
+        for (size_t i = 0; i < stages.size() * sizeof(StageRec); ++i) hsh = (hsh ^ q[i]) * 1099511628211ull;
+        for (int c2 : cand) hsh = (hsh ^ (unsigned)c2) * 1099511628211ull;
+        fprintf(stderr, "[kbmod_b200] tiled plan: schedule hash %016llx\n", hsh);
+    }
+    if (dbg)
         fprintf(stderr, "[kbmod_b200] tiled plan: N=%d tab=%d exact=%zu groups=%d stages=%d (+%zu single-image) "
                 "records=%lld of %lld max_sx=%d max_sy=%d w_base=%d w_step=%d rmax=%d sx_lim=%d sy_lim=%d\n", N, NTab,
                 exact.size(), n_groups, n_stages, stages_plain.size(), have_runs ? n_records[1] : n_records[0],
@@ -371,6 +420,7 @@ TiledPlan *tiled_plan_create(const StackView &sv, const kb_params &p, const floa
     if (!exact.empty())
         KB_CUDA(cudaMemcpyAsync(d + b_st + b_cand, exact.data(), exact.size() * 4, cudaMemcpyHostToDevice, st));
     KB_CUDA(cudaStreamSynchronize(st));  // the host vectors die with this scope
+    phase("upload");
     PlanView &v = plan->v;
     v.stages = (const StageRec *)d;
     v.cand = (const int *)(d + b_st);
