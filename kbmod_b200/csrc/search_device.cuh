@@ -585,19 +585,6 @@ __device__ __forceinline__ void evaluate_exact(const StackView &sv, const double
     }
 }
 
-// Number of valid observations along one trajectory (the obs_count of kernels.cu:195), by re-gathering.
-template <int NB>
-__device__ __forceinline__ int count_observations(const StackView &sv, const double *times, int x, int y, float vx,
-                                                  float vy) {
-    int seen = 0;
-    for (int t = 0; t < sv.T; ++t) {
-        const double tm = times[t];
-        float a, b;
-        if (load_pair<NB>(sv, t, predict_index(y, vy, tm), predict_index(x, vx, tm), a, b)) ++seen;
-    }
-    return seen;
-}
-
 // Ordering used for the per-pixel list when candidates are not visited in list order: higher lh first; equal lh
 // -> the candidate that comes first in the caller's list (what the reference's strict '>' insertion in list
 // order produces, kernels.cu:324-330).  Empty slots carry cand = -1 and therefore win ties, as they do in the

@@ -157,12 +157,6 @@ __device__ __forceinline__ int4 lds_v4(uint32_t addr) {
     return v;
 }
 template <int OFF>
-__device__ __forceinline__ int2 lds_v2(uint32_t addr) {
-    int2 v;
-    asm volatile("ld.shared.v2.s32 {%0, %1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(addr), "n"(OFF));
-    return v;
-}
-template <int OFF>
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     uint32_t w;
     asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(w) : "r"(addr), "n"(OFF));
